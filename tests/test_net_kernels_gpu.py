@@ -1,0 +1,231 @@
+"""Numerics of every `Net` kernel against the plain-PyTorch fp32/fp64 oracle."""
+import pytest
+import torch
+
+from csed_514_project_distributed_training_using_pytorch_b200.models import Net
+from csed_514_project_distributed_training_using_pytorch_b200.models import oracle
+from csed_514_project_distributed_training_using_pytorch_b200.ops import net_ops
+from csed_514_project_distributed_training_using_pytorch_b200.ops.fused import (
+    FusedNetEngine, X_F32, X_U8, X_U8_GATHER)
+
+pytestmark = pytest.mark.gpu
+
+RTOL, ATOL = 1e-4, 2e-5  # fp32 SIMT path; oracle is fp64 on CPU
+
+
+def _net(device, seed=1):
+    torch.manual_seed(seed)
+    return Net().to(device)
+
+
+def _oracle_params(net, dtype=torch.float64):
+    return [p.detach().cpu().to(dtype).requires_grad_(True) for p in net.param_list()]
+
+
+def _data(B, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    x = torch.randn(B, 1, 28, 28, generator=g)
+    y = torch.randint(0, 10, (B,), generator=g)
+    return x, y
+
+
+@pytest.mark.parametrize("B", [1, 8, 16, 32, 64, 1000])
+def test_layered_forward_eval(cuda_device, B):
+    net = _net(cuda_device).eval()
+    x, _ = _data(B)
+    with torch.no_grad():
+        got = net(x.to(cuda_device)).cpu()
+    want = oracle.net_forward(_oracle_params(net), x.double()).float()
+    torch.testing.assert_close(got, want.detach(), rtol=RTOL, atol=ATOL)
+
+
+@pytest.mark.parametrize("B", [1, 32, 64, 200])
+def test_layered_forward_backward_with_masks(cuda_device, B):
+    net = _net(cuda_device).train()
+    x, y = _data(B, seed=3)
+    m2, m3 = oracle.make_masks(B, torch.Generator().manual_seed(7))
+    for p in net.parameters():
+        p.grad = None
+    logp = net(x.to(cuda_device), masks=(m2.to(cuda_device), m3.to(cuda_device)))
+    loss = net_ops.nll_loss(logp, y.to(cuda_device))
+    loss.backward()
+
+    op = _oracle_params(net)
+    lo = oracle.net_loss(op, x.double(), y, m2.double(), m3.double())
+    lo.backward()
+    torch.testing.assert_close(loss.detach().cpu(), lo.detach().float(), rtol=RTOL, atol=ATOL)
+    for name, p, q in zip(Net.PARAM_ORDER, net.param_list(), op):
+        torch.testing.assert_close(p.grad.cpu(), q.grad.float(), rtol=2e-4, atol=2e-5,
+                                   msg=lambda m, n=name: f"{n}: {m}")
+
+
+def test_nll_sum_and_cross_entropy(cuda_device):
+    net = _net(cuda_device).eval()
+    x, y = _data(50)
+    with torch.no_grad():
+        logp = net(x.to(cuda_device))
+    s = net_ops.nll_loss(logp, y.to(cuda_device), size_average=False).cpu()
+    want = torch.nn.functional.nll_loss(logp.cpu(), y, reduction="sum")
+    torch.testing.assert_close(s, want, rtol=1e-5, atol=1e-5)
+    ce = net_ops.cross_entropy_on_log_probs(logp, y.to(cuda_device)).cpu()
+    want_ce = torch.nn.CrossEntropyLoss()(logp.cpu(), y)  # src/train_dist.py:67,82
+    torch.testing.assert_close(ce, want_ce, rtol=1e-5, atol=1e-6)
+
+
+def test_layered_dropout_statistics(cuda_device):
+    net = _net(cuda_device).train()
+    B = 512
+    x, _ = _data(B)
+    a1 = net_ops.conv1_pool_relu(x.to(cuda_device), net.conv1.weight, net.conv1.bias)
+    m2 = torch.empty(B, 20, device=cuda_device)
+    a2 = net_ops.conv2_drop_pool_relu(a1, net.conv2.weight, net.conv2.bias, m2, 1, 0.5, 123, 5)
+    vals = set(m2.unique().cpu().tolist())
+    assert vals <= {0.0, 2.0} and len(vals) == 2          # T9: {0, 1/(1-p)}
+    assert abs(m2.mean().item() - 1.0) < 0.06             # keep-probability 0.5
+    dropped = (m2 == 0).view(B, 20, 1, 1).expand_as(a2)
+    assert (a2[dropped] == 0).all()                       # whole channels are zeroed
+    m3 = torch.empty(B, 50, device=cuda_device)
+    net_ops.fc1_relu_drop(a2.view(B, 320), net.fc1.weight, net.fc1.bias, m3, 1, 0.5, 123, 5)
+    assert abs(m3.mean().item() - 1.0) < 0.05
+    # a different step gives a different mask, the same step the same mask
+    m2b = torch.empty(B, 20, device=cuda_device)
+    net_ops.conv2_drop_pool_relu(a1, net.conv2.weight, net.conv2.bias, m2b, 1, 0.5, 123, 6)
+    assert not torch.equal(m2, m2b)
+    m2c = torch.empty(B, 20, device=cuda_device)
+    net_ops.conv2_drop_pool_relu(a1, net.conv2.weight, net.conv2.bias, m2c, 1, 0.5, 123, 5)
+    assert torch.equal(m2, m2c)
+
+
+def test_gather_normalize_exact(cuda_device):
+    g = torch.Generator().manual_seed(0)
+    data = torch.randint(0, 256, (500, 784), dtype=torch.uint8, generator=g)
+    idx = torch.randint(0, 500, (64,), generator=g).to(torch.int32)
+    got = net_ops.gather_normalize(data.to(cuda_device), idx.to(cuda_device)).cpu()
+    want = oracle.normalize_u8(data[idx.long()])
+    assert torch.equal(got, want)  # same IEEE ops in the same order
+    got_all = net_ops.gather_normalize(data.to(cuda_device)).cpu()
+    assert torch.equal(got_all, oracle.normalize_u8(data))
+
+
+@pytest.mark.parametrize("B", [1, 8, 16, 32, 64, 200])
+def test_fused_step_matches_oracle(cuda_device, B):
+    """One whole step (forward, loss, backward, SGD) with injected masks == oracle."""
+    net = _net(cuda_device).train()
+    ref = _oracle_params(net)
+    eng = FusedNetEngine(net, lr=0.01, momentum=0.5)
+    bufs = [torch.zeros_like(p) for p in ref]
+    for it in range(3):
+        x, y = _data(B, seed=10 + it)
+        m2, m3 = oracle.make_masks(B, torch.Generator().manual_seed(20 + it))
+        eng.step(x.to(cuda_device), y.to(cuda_device),
+                 masks=(m2.to(cuda_device), m3.to(cuda_device)), write_grad=True)
+        for p in ref:
+            p.grad = None
+        lo = oracle.net_loss(ref, x.double(), y, m2.double(), m3.double())
+        lo.backward()
+        for name, gv, q in zip(Net.PARAM_ORDER, eng.flat.views(eng.flat.grad), ref):
+            torch.testing.assert_close(gv.cpu(), q.grad.float(), rtol=2e-4, atol=2e-5,
+                                       msg=lambda m, n=name: f"step {it} grad {n}: {m}")
+        oracle.sgd_momentum_step(ref, [q.grad for q in ref], bufs, 0.01, 0.5)
+        for name, p, q in zip(Net.PARAM_ORDER, net.param_list(), ref):
+            torch.testing.assert_close(p.detach().cpu(), q.detach().float(), rtol=1e-4, atol=1e-5,
+                                       msg=lambda m, n=name: f"step {it} param {n}: {m}")
+        got_loss = eng.last_losses(1)[0]
+        torch.testing.assert_close(got_loss, lo.detach().float(), rtol=1e-4, atol=1e-5)
+    assert eng.steps_done() == 3
+
+
+def test_fused_input_modes_agree(cuda_device):
+    g = torch.Generator().manual_seed(0)
+    data = torch.randint(0, 256, (300, 784), dtype=torch.uint8, generator=g)
+    labels = torch.randint(0, 10, (300,), generator=g)
+    idx = torch.randperm(300, generator=g)[:64].to(torch.int32)
+    xb = data[idx.long()]
+    yb = labels[idx.long()]
+    outs = []
+    for mode in (X_F32, X_U8, X_U8_GATHER):
+        net = _net(cuda_device).train()
+        eng = FusedNetEngine(net, dropout=False)
+        if mode == X_F32:
+            eng.step(oracle.normalize_u8(xb).to(cuda_device), yb.to(cuda_device), X_F32)
+        elif mode == X_U8:
+            eng.step(xb.to(cuda_device), yb.to(cuda_device), X_U8)
+        else:
+            eng.step(data.to(cuda_device), labels.to(cuda_device), X_U8_GATHER,
+                     gidx=idx.to(cuda_device))
+        outs.append(eng.flat.param.clone())
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
+
+
+def test_fused_graph_replay_equals_eager(cuda_device):
+    B = 64
+    xs = [_data(B, seed=s) for s in range(5)]
+    # eager
+    net_a = _net(cuda_device).train()
+    eng_a = FusedNetEngine(net_a, seed=9)
+    for x, y in xs:
+        eng_a.step(x.to(cuda_device), y.to(cuda_device))
+    # graph
+    net_b = _net(cuda_device).train()
+    eng_b = FusedNetEngine(net_b, seed=9)
+    sx = torch.empty(B, 1, 28, 28, device=cuda_device)
+    sy = torch.empty(B, dtype=torch.int64, device=cuda_device)
+    sx.copy_(xs[0][0]); sy.copy_(xs[0][1])
+    graph = eng_b.capture(sx, sy)
+    assert eng_b.steps_done() == 0  # capture leaves the state untouched
+    for x, y in xs:
+        sx.copy_(x); sy.copy_(y)
+        graph.replay()
+    torch.cuda.synchronize()
+    assert eng_b.steps_done() == 5
+    assert torch.equal(eng_a.flat.param, eng_b.flat.param)  # same kernels, same masks: bit-equal
+    assert torch.equal(eng_a.last_losses(5), eng_b.last_losses(5))
+    # parameters are views of the flat buffer, so the module sees the update
+    assert torch.equal(net_b.fc2.bias.detach(), eng_b.flat.views(eng_b.flat.param)[7])
+
+
+def test_fused_is_deterministic(cuda_device):
+    x, y = _data(64, seed=4)
+    res = []
+    for _ in range(2):
+        net = _net(cuda_device).train()
+        eng = FusedNetEngine(net, seed=3)
+        for _ in range(4):
+            eng.step(x.to(cuda_device), y.to(cuda_device))
+        res.append(eng.flat.param.clone())
+    assert torch.equal(res[0], res[1])
+
+
+def test_eval_kernel(cuda_device):
+    net = _net(cuda_device).eval()
+    eng = FusedNetEngine(net)
+    x, y = _data(1000, seed=5)
+    logp = torch.empty(1000, 10, device=cuda_device)
+    out = eng.evaluate_batch(x.to(cuda_device), y.to(cuda_device), logp_out=logp).cpu()
+    want = oracle.net_forward(_oracle_params(net), x.double()).float().detach()
+    torch.testing.assert_close(logp.cpu(), want, rtol=RTOL, atol=ATOL)
+    want_loss = torch.nn.functional.nll_loss(want, y, reduction="sum")  # src/train.py:94
+    want_correct = (want.argmax(1) == y).sum()                           # src/train.py:95-96
+    torch.testing.assert_close(out[0], want_loss, rtol=1e-4, atol=1e-3)
+    assert int(out[1].item()) == int(want_correct)
+    out2 = eng.evaluate_batch(x.to(cuda_device), y.to(cuda_device), accumulate=True).cpu()
+    assert int(out2[1].item()) == 2 * int(want_correct)
+
+
+def test_sgd_kernel_matches_torch(cuda_device):
+    from csed_514_project_distributed_training_using_pytorch_b200.ops.sgd import FlatSGD
+    torch.manual_seed(0)
+    n = 4096 + 8
+    p = torch.randn(n)
+    ref_p = p.clone().requires_grad_(True)
+    opt = torch.optim.SGD([ref_p], lr=0.02, momentum=0.5)
+    dp = p.to(cuda_device)
+    dg = torch.zeros(n, device=cuda_device)
+    sgd = FlatSGD(dp, dg, lr=0.02, momentum=0.5)
+    for _ in range(4):
+        g = torch.randn(n)
+        ref_p.grad = g.clone()
+        opt.step()
+        dg.copy_(g)
+        sgd.step()
+    torch.testing.assert_close(dp.cpu(), ref_p.detach(), rtol=1e-6, atol=1e-6)
