@@ -138,17 +138,25 @@ __device__ __forceinline__ void conv2_fwd_img(const float* __restrict__ a1s,
 
 // fc1 + bias + ReLU + element dropout (src/model.py:19-20).
 // a2s[320] -> h1s[50]; W3 is read from global (L2-resident, coalesced).
+// W_SMEM: W3 has been staged in shared memory (fused step); otherwise it is global.
+template <bool W_SMEM>
 __device__ __forceinline__ void fc1_fwd_img(const float* __restrict__ a2s,
                                             const float* __restrict__ W3,
                                             const float* __restrict__ b3,
                                             const float* __restrict__ m3s,
                                             float* __restrict__ h1s) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  for (int j = warp; j < FC1; j += NT / 32) {
+  float av[A2_SZ / 32];
+#pragma unroll
+  for (int i = 0; i < A2_SZ / 32; ++i) av[i] = a2s[lane + 32 * i];
+#pragma unroll
+  for (int jj = 0; jj < FC1 / (NT / 32); ++jj) {
+    const int j = warp + jj * (NT / 32);
     const float* w = W3 + j * A2_SZ;
     float s = 0.0f;
 #pragma unroll
-    for (int i = 0; i < A2_SZ / 32; ++i) s = fmaf(a2s[lane + 32 * i], __ldg(w + lane + 32 * i), s);
+    for (int i = 0; i < A2_SZ / 32; ++i)
+      s = fmaf(av[i], W_SMEM ? w[lane + 32 * i] : __ldg(w + lane + 32 * i), s);
     s = warp_sum(s);
     if (lane == 0) h1s[j] = fmaxf(s + __ldg(b3 + j), 0.0f) * m3s[j];
   }
@@ -210,6 +218,7 @@ __device__ __forceinline__ void fc2_bwd_img(const float* __restrict__ dlog_s,
 
 // fc1 backward: dpre_s[50], a2s[320] -> dW3, db3 partials and
 // g2s[320] = gradient w.r.t. conv2's pooled pre-ReLU map (ReLU and channel mask applied).
+template <bool W_SMEM>
 __device__ __forceinline__ void fc1_bwd_img(const float* __restrict__ dpre_s,
                                             const float* __restrict__ a2s,
                                             const float* __restrict__ m2s,
@@ -223,7 +232,7 @@ __device__ __forceinline__ void fc1_bwd_img(const float* __restrict__ dpre_s,
   for (int j = 0; j < FC1; ++j) {
     const float d = dpre_s[j];
     gacc(gW3 + j * A2_SZ + t, d * a, first);
-    da = fmaf(d, __ldg(W3 + j * A2_SZ + t), da);
+    da = fmaf(d, W_SMEM ? W3[j * A2_SZ + t] : __ldg(W3 + j * A2_SZ + t), da);
   }
   g2s[t] = (a > 0.0f) ? da * m2s[t >> 4] : 0.0f;
   if (t < FC1) gacc(gB3 + t, dpre_s[t], first);
@@ -316,6 +325,231 @@ __device__ __forceinline__ void conv1_bwd_img(const float* __restrict__ g1s,
     for (int p = 0; p < 144; ++p) s += g[p];
     gacc(gB1 + (t - 256), s, first);
   }
+}
+
+
+// ---- sparse backward (fused step) -------------------------------------------
+// After dropout2d and the ReLUs most of the 320 conv2 window gradients are exactly
+// zero (half the channels are dropped outright), and so are about half of conv1's
+// 1440. The fused step compacts the non-zeros into small lists first and lets the
+// wgrad / dgrad loops run over list lengths instead of fixed 16 / 144 / 3x3x20 trips.
+
+struct SparseLists {
+  int* nzc_cnt;      // [20]      non-zeros per conv2 output channel
+  uint8_t* nzc_pos;  // [20][16]  their Y*12+X inside a1's 12x12 frame
+  float* nzc_g;      // [20][16]
+  int* lst_cnt;      // [64]      non-zeros per conv2 output position (8x8)
+  uint8_t* lst_co;   // [64][20]  their output channel
+  float* lst_g;      // [64][20]
+  int* cnt1;         // [10]      non-zeros per conv1 channel after in-place compaction
+};
+constexpr int SPARSE_LIST_BYTES = 20 * 4 + 320 + 320 * 4 + 64 * 4 + 1280 + 1280 * 4 + 16 * 4;
+
+__device__ __forceinline__ SparseLists carve_lists(void* base) {
+  SparseLists L;
+  float* f = reinterpret_cast<float*>(base);
+  L.nzc_g = f; f += 320;
+  L.lst_g = f; f += 1280;
+  L.nzc_cnt = reinterpret_cast<int*>(f); f += 20;
+  L.lst_cnt = reinterpret_cast<int*>(f); f += 64;
+  L.cnt1 = reinterpret_cast<int*>(f); f += 16;
+  uint8_t* b = reinterpret_cast<uint8_t*>(f);
+  L.nzc_pos = b; b += 320;
+  L.lst_co = b;
+  return L;
+}
+
+__device__ __forceinline__ void build_conv2_lists(const float* __restrict__ g2s,
+                                                  const uint8_t* __restrict__ pos2s,
+                                                  const SparseLists& L) {
+  const int t = threadIdx.x, lane = t & 31;
+  {  // per channel: warp w owns channels 2w, 2w+1 (16 lanes each); t == co*16 + p
+    const float g = g2s[t];
+    const unsigned nz = __ballot_sync(0xffffffffu, g != 0.0f);
+    const unsigned half = (lane >> 4) ? (nz >> 16) : (nz & 0xffffu);
+    const int rank = __popc(half & ((1u << (lane & 15)) - 1u));
+    const int co = t >> 4;
+    if (g != 0.0f) {
+      L.nzc_pos[co * 16 + rank] = pos2s[t];
+      L.nzc_g[co * 16 + rank] = g;
+    }
+    if ((lane & 15) == 0) L.nzc_cnt[co] = __popc(half);
+  }
+  if (t < 64) {  // per conv2 output position: which channels put their window max here
+    const int Y = t >> 3, X = t & 7;
+    const int p = (Y >> 1) * 4 + (X >> 1);
+    const int pos12 = Y * 12 + X;
+    int n = 0;
+#pragma unroll 4
+    for (int co = 0; co < C2; ++co) {
+      const float g = g2s[co * 16 + p];
+      if (pos2s[co * 16 + p] == pos12 && g != 0.0f) {
+        L.lst_co[t * 20 + n] = (uint8_t)co;
+        L.lst_g[t * 20 + n] = g;
+        ++n;
+      }
+    }
+    L.lst_cnt[t] = n;
+  }
+}
+
+// conv2 backward over the compacted lists: wgrad, bias grad, and phase 1 of dgrad into
+// T[64][250] (shared memory).
+__device__ __forceinline__ void conv2_bwd_sparse_img(const SparseLists& L,
+                                                     const float* __restrict__ a1s,
+                                                     const float* __restrict__ w2s,
+                                                     float* __restrict__ T,
+                                                     float* __restrict__ gW2,
+                                                     float* __restrict__ gB2, bool first) {
+  const int t = threadIdx.x;
+  if (t < 250) {
+    // thread <-> one (ci, tap) column r of W2 / T; channel and position loops are
+    // uniform across the CTA, list reads are broadcasts.
+    const int r = t;
+    const int ci = r / 25, kk = r - ci * 25;
+    const int ky = kk / 5, kx = kk - ky * 5;
+    const float* a = a1s + ci * 144 + ky * 12 + kx;
+#pragma unroll 1
+    for (int co = 0; co < C2; ++co) {
+      const int n = L.nzc_cnt[co];
+      if (n == 0 && !first) continue;
+      const float* g = L.nzc_g + co * 16;
+      const uint8_t* ps = L.nzc_pos + co * 16;
+      float s = 0.0f;
+      for (int e = 0; e < n; ++e) s = fmaf(g[e], a[ps[e]], s);
+      gacc(gW2 + co * 250 + r, s, first);
+    }
+    // dgrad, phase 1: T[pos][r] = sum over the channels whose window max sits at conv
+    // position `pos` of g * W2[co][ci][tap] (zero for positions nobody selected).
+#pragma unroll 1
+    for (int pos = 0; pos < 64; ++pos) {
+      const int n = L.lst_cnt[pos];
+      const float* g = L.lst_g + pos * 20;
+      const uint8_t* cs = L.lst_co + pos * 20;
+      float s = 0.0f;
+      for (int e = 0; e < n; ++e) s = fmaf(g[e], w2s[(int)cs[e] * 250 + r], s);
+      T[pos * 250 + r] = s;
+    }
+  } else if (t >= 256 && t < 256 + C2) {
+    const int co = t - 256;
+    const int n = L.nzc_cnt[co];
+    float s = 0.0f;
+    for (int e = 0; e < n; ++e) s += L.nzc_g[co * 16 + e];
+    gacc(gB2 + co, s, first);
+  }
+}
+
+// dgrad, phase 2 (after a barrier): g1s[ci][u][v] = sum over the <=25 filter taps of
+// T[(u-ky, v-kx)][ci][tap], with conv1's ReLU mask folded in.
+__device__ __forceinline__ void conv2_dgrad_gather_img(const float* __restrict__ T,
+                                                       const float* __restrict__ a1s,
+                                                       float* __restrict__ g1s) {
+  for (int q = threadIdx.x; q < A1_SZ; q += NT) {
+    const int ci = q / 144, r = q - ci * 144;
+    const int u = r / 12, v = r - u * 12;
+    float s = 0.0f;
+    if (a1s[q] > 0.0f) {
+      // (Y*8+X)*250 + ci*25 + tap with Y=u-ky, X=v-kx is base - ky*1995 - kx*249:
+      // every tap is a compile-time offset from one base address.
+      const float* tb = T + (u * 8 + v) * 250 + ci * 25;
+#pragma unroll
+      for (int ky = 0; ky < 5; ++ky) {
+        const bool oky = (unsigned)(u - ky) < 8u;
+#pragma unroll
+        for (int kx = 0; kx < 5; ++kx) {
+          const bool ok = oky && ((unsigned)(v - kx) < 8u);
+          if (ok) s += tb[-ky * 1995 - kx * 249];
+        }
+      }
+    }
+    g1s[q] = s;
+  }
+}
+
+// In-place compaction of conv1's window gradients: warp c squeezes channel c's
+// non-zeros (value + position) to the front of its 144-entry segment.
+__device__ __forceinline__ void compact_conv1_grads(float* __restrict__ g1s,
+                                                    uint16_t* __restrict__ pos1s,
+                                                    const SparseLists& L) {
+  const int c = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (c >= C1) return;
+  float* g = g1s + c * 144;
+  uint16_t* ps = pos1s + c * 144;
+  int off = 0;
+  for (int base = 0; base < 144; base += 32) {
+    const int i = base + lane;
+    const float gv = (i < 144) ? g[i] : 0.0f;
+    const uint16_t pv = (i < 144) ? ps[i] : (uint16_t)0;
+    const unsigned nz = __ballot_sync(0xffffffffu, gv != 0.0f);
+    const int rank = __popc(nz & ((1u << lane) - 1u));
+    __syncwarp();
+    if (gv != 0.0f) { g[off + rank] = gv; ps[off + rank] = pv; }
+    off += __popc(nz);
+    __syncwarp();
+  }
+  if (lane == 0) L.cnt1[c] = off;
+}
+
+__device__ __forceinline__ void conv1_bwd_sparse_img(const SparseLists& L,
+                                                     const float* __restrict__ g1s,
+                                                     const uint16_t* __restrict__ pos1s,
+                                                     const float* __restrict__ xs,
+                                                     float* __restrict__ gW1,
+                                                     float* __restrict__ gB1, bool first) {
+  const int t = threadIdx.x;
+  if (t < W1_SZ) {
+    const int c = t / 25, kk = t - c * 25;
+    const int ky = kk / 5, kx = kk - ky * 5;
+    const float* x = xs + ky * IMG + kx;
+    const float* g = g1s + c * 144;
+    const uint16_t* ps = pos1s + c * 144;
+    const int n = L.cnt1[c];
+    float s0 = 0.0f, s1 = 0.0f, s2 = 0.0f, s3 = 0.0f;
+    int e = 0;
+    for (; e + 3 < n; e += 4) {  // 16-byte value and 8-byte position broadcasts
+      const float4 gv = *reinterpret_cast<const float4*>(g + e);
+      const uint2 pp = *reinterpret_cast<const uint2*>(ps + e);
+      s0 = fmaf(gv.x, x[pp.x & 0xffffu], s0);
+      s1 = fmaf(gv.y, x[pp.x >> 16], s1);
+      s2 = fmaf(gv.z, x[pp.y & 0xffffu], s2);
+      s3 = fmaf(gv.w, x[pp.y >> 16], s3);
+    }
+    for (; e < n; ++e) s0 = fmaf(g[e], x[ps[e]], s0);
+    gacc(gW1 + t, (s0 + s1) + (s2 + s3), first);
+  } else if (t >= 256 && t < 256 + C1) {
+    const int c = t - 256;
+    const int n = L.cnt1[c];
+    float s = 0.0f;
+    for (int e = 0; e < n; ++e) s += g1s[c * 144 + e];
+    gacc(gB1 + c, s, first);
+  }
+}
+
+// Fixed-order sum of G gradient partial rows for one float4 column, spread over the 8
+// row-groups of a 256-thread CTA (32 columns x 8 groups) so all loads are in flight at
+// once. The result is valid in the threads of row-group 0.
+__device__ __forceinline__ float4 sum_partial_rows_256(const float* __restrict__ partial, int G,
+                                                       int stride, int col4, bool valid,
+                                                       float4 (*sm)[32]) {
+  const int c = threadIdx.x & 31, rg = threadIdx.x >> 5;
+  float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (valid) {
+#pragma unroll 4
+    for (int r = rg; r < G; r += 8) {
+      const float4 v = __ldcg(reinterpret_cast<const float4*>(partial + (size_t)r * stride) + col4);
+      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+    }
+  }
+  sm[rg][c] = s;
+  __syncthreads();
+  if (rg == 0) {
+#pragma unroll
+    for (int k = 1; k < 8; ++k) {
+      const float4 v = sm[k][c];
+      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+    }
+  }
+  return s;
 }
 
 }  // namespace net

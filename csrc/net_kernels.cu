@@ -249,7 +249,7 @@ fc1_fwd_kernel(const float* __restrict__ a2, const float* __restrict__ W3,
       m3s[t] = m;
     }
     __syncthreads();
-    fc1_fwd_img(a2s, W3, b3, m3s, h1s);
+    fc1_fwd_img<false>(a2s, W3, b3, m3s, h1s);
     __syncthreads();
     if (t < FC1) h1[(size_t)img * FC1 + t] = h1s[t];
   }
@@ -428,7 +428,12 @@ struct FusedSmem {
 constexpr int FUSED_SMEM_FLOATS = IMG_SZ + A1_SZ + A2_SZ + 64 + 64 + 32 + 16 + 16 + 64 + A2_SZ +
                                   A1_SZ + 252 + 12 + W2_SZ + 20 + W4_SZ + 12 + A1_SZ / 2 +
                                   A2_SZ / 4;
-constexpr int FUSED_SMEM_BYTES = FUSED_SMEM_FLOATS * 4;
+constexpr int FUSED_LIST_OFF = FUSED_SMEM_FLOATS * 4;
+constexpr int FUSED_T_OFF = FUSED_LIST_OFF + SPARSE_LIST_BYTES;      // T[64][250] floats
+constexpr int FUSED_W3_OFF = FUSED_T_OFF + 64 * 250 * 4;             // fc1.weight staged in smem
+constexpr int FUSED_SMEM_BYTES = FUSED_W3_OFF + W3_SZ * 4;           // ~181 KB: one CTA per SM
+constexpr int EVAL_SMEM_BYTES = FUSED_SMEM_FLOATS * 4;
+static_assert(FUSED_T_OFF % 16 == 0 && FUSED_W3_OFF % 16 == 0, "smem carve alignment");
 
 __device__ __forceinline__ FusedSmem carve(float* s) {
   FusedSmem f;
@@ -480,7 +485,16 @@ net_fwdbwd_kernel(const float* __restrict__ params, const void* __restrict__ x, 
                   unsigned sample_base, int idx_stride) {
   extern __shared__ __align__(16) float smem[];
   const FusedSmem f = carve(smem);
+  const SparseLists L = carve_lists(smem + FUSED_SMEM_FLOATS);
+  float* Ts = reinterpret_cast<float*>(reinterpret_cast<char*>(smem) + FUSED_T_OFF);
+  float* w3s = reinterpret_cast<float*>(reinterpret_cast<char*>(smem) + FUSED_W3_OFF);
   const int t = threadIdx.x;
+  // fc1.weight (64 KB) streams into shared memory with cp.async while conv1/conv2 run
+  for (int i = t; i < W3_SZ / 4; i += NT) {
+    const unsigned dst = (unsigned)__cvta_generic_to_shared(w3s + i * 4);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(params + OFF_W3 + i * 4));
+  }
+  asm volatile("cp.async.commit_group;" ::: "memory");
   load_weights(f, params);
   const unsigned long long step = step_ptr ? step_ptr[0] : 0ull;
   if (idx_stride != 0 && step_ptr) gidx += (size_t)(step - step_ptr[1]) * (size_t)idx_stride;
@@ -514,8 +528,9 @@ net_fwdbwd_kernel(const float* __restrict__ params, const void* __restrict__ x, 
     conv1_fwd_img(f.xs, f.w1s, f.b1s, f.a1s, f.pos1s);
     __syncthreads();
     conv2_fwd_img(f.a1s, f.w2s, f.b2s, f.m2s, f.a2s, f.pos2s);
+    if (first) asm volatile("cp.async.wait_all;" ::: "memory");
     __syncthreads();
-    fc1_fwd_img(f.a2s, params + OFF_W3, params + OFF_B3, f.m3s, f.h1s);
+    fc1_fwd_img<true>(f.a2s, w3s, params + OFF_B3, f.m3s, f.h1s);
     __syncthreads();
     fc2_fwd_img(f.h1s, f.w4s, f.b4s, f.logit_s);
     __syncthreads();
@@ -525,19 +540,28 @@ net_fwdbwd_kernel(const float* __restrict__ params, const void* __restrict__ x, 
       log_softmax10(f.logit_s, lp);
       const int row_lab = (x_mode >= 2) ? gidx[img] : img;
       const int tgt = (int)labels[row_lab];
-      loss_acc -= lp[tgt] * inv_B;
+      float lt = 0.0f;
 #pragma unroll
-      for (int c = 0; c < NCLS; ++c)
+      for (int c = 0; c < NCLS; ++c) {
+        if (c == tgt) lt = lp[c];
         f.dlog_s[c] = (expf(lp[c]) - (c == tgt ? 1.0f : 0.0f)) * inv_B;
+      }
+      loss_acc -= lt * inv_B;
     }
     __syncthreads();
     fc2_bwd_img(f.dlog_s, f.h1s, f.m3s, f.w4s, f.dpre_s, row + OFF_W4, row + OFF_B4, first);
     __syncthreads();
-    fc1_bwd_img(f.dpre_s, f.a2s, f.m2s, params + OFF_W3, f.g2s, row + OFF_W3, row + OFF_B3, first);
+    fc1_bwd_img<true>(f.dpre_s, f.a2s, f.m2s, w3s, f.g2s, row + OFF_W3, row + OFF_B3, first);
     __syncthreads();
-    conv2_bwd_img<true>(f.g2s, f.pos2s, f.a1s, f.w2s, f.g1s, row + OFF_W2, row + OFF_B2, first, true);
+    build_conv2_lists(f.g2s, f.pos2s, L);
     __syncthreads();
-    conv1_bwd_img(f.g1s, f.pos1s, f.xs, row + OFF_W1, row + OFF_B1, first);
+    conv2_bwd_sparse_img(L, f.a1s, f.w2s, Ts, row + OFF_W2, row + OFF_B2, first);
+    __syncthreads();
+    conv2_dgrad_gather_img(Ts, f.a1s, f.g1s);
+    __syncthreads();
+    compact_conv1_grads(f.g1s, f.pos1s, L);
+    __syncthreads();
+    conv1_bwd_sparse_img(L, f.g1s, f.pos1s, f.xs, row + OFF_W1, row + OFF_B1, first);
     __syncthreads();
   }
   if (t == 0) loss_partial[blockIdx.x] = loss_acc;
@@ -551,20 +575,16 @@ net_fwdbwd_kernel(const float* __restrict__ params, const void* __restrict__ x, 
 // Fused whole-step kernel B (single GPU): fixed-order sum of the partial rows, then
 // SGD-momentum in place (K14+K15: no zero_grad pass, gradients never hit .grad unless asked).
 // The multi-GPU version with the all-reduce in the middle lives in comm_kernels.cu.
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(256)
 net_reduce_sgd_kernel(const float* __restrict__ partial, int G, float* __restrict__ params,
                       float* __restrict__ mom, float* __restrict__ grad_out,
                       const float* __restrict__ hp, const float* __restrict__ loss_partial,
                       float* __restrict__ loss_ring, int ring, unsigned long long* step_ptr) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  __shared__ float4 sm[8][32];
   constexpr int N4 = FLAT_SZ / 4;
-  if (i < N4) {
-    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll 8
-    for (int r = 0; r < G; ++r) {
-      const float4 v = __ldcg(reinterpret_cast<const float4*>(partial + (size_t)r * FLAT_SZ) + i);
-      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
-    }
+  const int i = blockIdx.x * 32 + (threadIdx.x & 31);
+  const float4 s = sum_partial_rows_256(partial, G, FLAT_SZ, i, i < N4, sm);
+  if (threadIdx.x < 32 && i < N4) {
     if (grad_out) reinterpret_cast<float4*>(grad_out)[i] = s;
     if (params) {
       const float lr = hp[0], mu = hp[1];
@@ -576,7 +596,7 @@ net_reduce_sgd_kernel(const float* __restrict__ partial, int G, float* __restric
       reinterpret_cast<float4*>(mom)[i] = bv;
     }
   }
-  if (blockIdx.x == 0 && threadIdx.x == 0) {
+  if (blockIdx.x == 0 && threadIdx.x == 64) {
     float l = 0.0f;
     for (int r = 0; r < G; ++r) l += loss_partial[r];
     const unsigned long long step = step_ptr ? *step_ptr : 0ull;
@@ -607,7 +627,7 @@ net_eval_kernel(const float* __restrict__ params, const void* __restrict__ x, in
     __syncthreads();
     conv2_fwd_img(f.a1s, f.w2s, f.b2s, f.m2s, f.a2s, f.pos2s);
     __syncthreads();
-    fc1_fwd_img(f.a2s, params + OFF_W3, params + OFF_B3, f.m3s, f.h1s);
+    fc1_fwd_img<false>(f.a2s, params + OFF_W3, params + OFF_B3, f.m3s, f.h1s);
     __syncthreads();
     fc2_fwd_img(f.h1s, f.w4s, f.b4s, f.logit_s);
     __syncthreads();
@@ -623,7 +643,10 @@ net_eval_kernel(const float* __restrict__ params, const void* __restrict__ x, in
       if (labels) {
         const int row_lab = (x_mode >= 2) ? gidx[img] : img;
         const int tgt = (int)labels[row_lab];
-        loss_img[img] = -lp[tgt];
+        float lt = 0.0f;
+#pragma unroll
+        for (int c = 0; c < NCLS; ++c) if (c == tgt) lt = lp[c];
+        loss_img[img] = -lt;
         pred_img[img] = (best == tgt) ? 1 : 0;
       }
     }
@@ -798,7 +821,7 @@ static int ensure_fused_attr() {
     B200_CUDA_OK(cudaFuncSetAttribute(net_fwdbwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       FUSED_SMEM_BYTES));
     B200_CUDA_OK(cudaFuncSetAttribute(net_eval_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      FUSED_SMEM_BYTES));
+                                      EVAL_SMEM_BYTES));
     done = true;
   }
   return 0;
@@ -826,8 +849,8 @@ int b200_net_reduce_sgd(const float* partial, int rows, float* params, float* mo
                         const float* hp, const float* loss_partial, float* loss_ring, int ring,
                         unsigned long long* step_ptr, void* stream) {
   B200_REQUIRE(rows > 0 && rows <= 148, "b200_net_reduce_sgd: rows out of range");
-  const int blocks = (FLAT_SZ / 4 + 127) / 128;
-  net_reduce_sgd_kernel<<<blocks, 128, 0, (cudaStream_t)stream>>>(
+  const int blocks = (FLAT_SZ / 4 + 31) / 32;
+  net_reduce_sgd_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(
       partial, rows, params, mom, grad_out, hp, loss_partial, loss_ring, ring, step_ptr);
   B200_LAUNCH_OK();
   return 0;
@@ -839,7 +862,7 @@ int b200_net_eval(const float* params, const void* x, int x_mode, const long lon
   if (B <= 0) return 0;
   if (int e = ensure_fused_attr()) return e;
   B200_REQUIRE(!labels || (loss_img && pred_img), "b200_net_eval: labels need loss/pred buffers");
-  net_eval_kernel<<<grid_for(B, 148 * 4), NT, FUSED_SMEM_BYTES, (cudaStream_t)stream>>>(
+  net_eval_kernel<<<grid_for(B, 148 * 4), NT, EVAL_SMEM_BYTES, (cudaStream_t)stream>>>(
       params, x, x_mode, labels, gidx, B, logp_out, loss_img, pred_img);
   B200_LAUNCH_OK();
   if (labels && out2) {
