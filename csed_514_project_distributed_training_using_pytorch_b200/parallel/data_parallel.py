@@ -1,0 +1,109 @@
+"""DataParallel: the `DDP(model)` of the reference (src/train_dist.py:63), B200-native.
+
+Construction: verifies that every rank holds the same parameter shapes,
+re-homes the parameters and their gradients into flat symmetric buffers, and broadcasts
+rank 0's values with the peer-memory broadcast kernel (K16), so ranks seeded differently
+start identical. Backward (T3): post-accumulate-grad hooks mark gradients ready; the
+reducer launches one fused all-reduce kernel per complete bucket on a side stream while
+backward continues; `.grad` holds the mean over ranks before `optimizer.step()`.
+Evaluation / `torch.no_grad()` forwards do no synchronisation and no bookkeeping (T4).
+`no_sync()` skips the reduction for gradient accumulation.
+
+For the reference network there is a faster door: `fused_engine()` returns a
+`FusedNetEngine` whose kernel B does partial-row sum + all-reduce + SGD in one launch.
+"""
+from __future__ import annotations
+
+import contextlib
+from typing import Optional, Sequence
+
+import torch
+from torch import nn
+
+from ..utils.flat import FlatParams
+from .reducer import Reducer
+
+
+class DataParallel(nn.Module):
+    def __init__(self, module: nn.Module, comm=None, bucket_of: Optional[Sequence[int]] = None,
+                 fuse_sgd=None, algo="auto", broadcast_from: int = 0):
+        super().__init__()
+        if comm is None:
+            from .process_group import get_comm
+            comm = get_comm()
+        self.module = module
+        self.comm = comm
+        self._verify_shapes()
+        self.flat = FlatParams(module, alloc=comm.alloc)
+        # init_sync: rank 0's parameters (and buffers) win (torch DDP default)
+        if comm.world_size > 1:
+            comm.broadcast(self.flat.param, root=broadcast_from)
+            for buf in module.buffers():
+                comm.broadcast(buf, root=broadcast_from)
+        self.reducer = Reducer(self.flat, comm, bucket_of=bucket_of, fuse_sgd=fuse_sgd, algo=algo)
+        self._params = list(module.parameters())
+        self._require_backward_sync = True
+        self._pass_open = False
+        for i, p in enumerate(self._params):
+            if p.requires_grad:
+                p.register_post_accumulate_grad_hook(self._make_hook(i))
+
+    def _verify_shapes(self):
+        shapes = [tuple(p.shape) for p in self.module.parameters()]
+        all_shapes = self.comm.all_gather_object(shapes)
+        for r, s in enumerate(all_shapes):
+            if s != all_shapes[0]:
+                raise RuntimeError(f"parameter shapes differ between rank 0 and rank {r}")
+
+    def _make_hook(self, i: int):
+        def hook(param):
+            if not (self._require_backward_sync and self._pass_open):
+                return
+            # autograd may have rebound .grad to a fresh tensor: move it into the bucket
+            s = self.flat.slots[i]
+            slot = self.flat.grad[s.offset:s.offset + s.numel].view(s.shape)
+            if param.grad is not None and param.grad.data_ptr() != slot.data_ptr():
+                slot.copy_(param.grad)
+                param.grad = slot
+            self.reducer.mark_ready(i)
+            if self.reducer.core.all_done():
+                self.reducer.finalize_backward()
+                self._pass_open = False
+        return hook
+
+    def forward(self, *args, **kwargs):
+        if torch.is_grad_enabled() and self.training and self._require_backward_sync:
+            # make sure the previous step's (fused) update is visible to this forward
+            if self.reducer.is_cuda:
+                torch.cuda.current_stream().wait_stream(self.reducer.stream)
+            self.reducer.prepare_for_backward()
+            self._pass_open = True
+        return self.module(*args, **kwargs)
+
+    @contextlib.contextmanager
+    def no_sync(self):
+        """Accumulate gradients locally (no all-reduce) inside the context."""
+        old = self._require_backward_sync
+        self._require_backward_sync = False
+        try:
+            yield
+        finally:
+            self._require_backward_sync = old
+
+    def zero_grad(self, set_to_none: bool = False):
+        """Gradients live in the flat bucket: zero in place and keep the views bound."""
+        self.flat.grad.zero_()
+        self.flat.rebind_grads()
+
+    def fused_engine(self, lr: float, momentum: float, seed: int = 1, **kw):
+        """The two-kernel fused step for models.Net with the all-reduce inside kernel B."""
+        from ..ops.fused import FusedNetEngine
+        return FusedNetEngine(self.module, lr=lr, momentum=momentum, seed=seed, comm=self.comm,
+                              flat=self.flat, **kw)
+
+    def state_dict(self, *a, **k):
+        """The UNWRAPPED module's state_dict: no `module.` prefix (src/train_dist.py:116,164)."""
+        return self.module.state_dict(*a, **k)
+
+    def load_state_dict(self, sd, *a, **k):
+        return self.module.load_state_dict(sd, *a, **k)

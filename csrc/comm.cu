@@ -1,0 +1,572 @@
+// Communication runtime + collective kernels over NVSwitch peer memory (SURVEY §5.1,
+// rows 8.10-8.14, 8.18). Replaces the reference's Gloo/TCP backend
+// (src/train_dist.py:144-146; implicit broadcast at :63, implicit all-reduce at :83;
+// send/recv at src/run1.py:13,16).
+//
+// Host side: symmetric arena allocation and cudaIpc handle export/import.
+// Device side, all push-based (posted stores over NVLink, no remote-read round trips):
+//   comm_barrier_kernel                 flag barrier across ranks
+//   comm_broadcast_kernel               root's buffer -> every rank (DDP init, K16)
+//   comm_send_kernel / comm_recv_kernel mailbox + flag point-to-point (K20)
+//   net_reduce_allreduce_sgd_kernel     Net's kernel B: partial-row sum + one-shot
+//                                       all-reduce + 1/world + SGD-momentum (K17+K15)
+//   allreduce_kernel<T, ALGO, UPDATE>   generic bucket all-reduce, one-shot or two-shot
+//                                       (reduce-scatter + all-gather), optionally fused
+//                                       with the sharded SGD-momentum update
+#include <cuda_bf16.h>
+
+#include <cstring>
+
+#include "comm.cuh"
+#include "net_device.cuh"
+
+using namespace net;
+
+// ===========================================================================
+// Host: symmetric memory
+// ===========================================================================
+extern "C" {
+
+int b200_symm_alloc(size_t bytes, void** dptr, unsigned char* handle64) {
+  B200_REQUIRE(bytes > 0 && dptr && handle64, "b200_symm_alloc: bad arguments");
+  void* p = nullptr;
+  B200_CUDA_OK(cudaMalloc(&p, bytes));
+  B200_CUDA_OK(cudaMemset(p, 0, bytes));
+  cudaIpcMemHandle_t h;
+  B200_CUDA_OK(cudaIpcGetMemHandle(&h, p));
+  static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t is 64 bytes");
+  memcpy(handle64, &h, 64);
+  B200_CUDA_OK(cudaDeviceSynchronize());
+  *dptr = p;
+  return 0;
+}
+
+int b200_symm_open(const unsigned char* handle64, void** peer_ptr_out) {
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, 64);
+  void* p = nullptr;
+  B200_CUDA_OK(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+  *peer_ptr_out = p;
+  return 0;
+}
+
+int b200_symm_close(void* peer_ptr_in) {
+  B200_CUDA_OK(cudaIpcCloseMemHandle(peer_ptr_in));
+  return 0;
+}
+
+int b200_symm_free(void* dptr) {
+  B200_CUDA_OK(cudaFree(dptr));
+  return 0;
+}
+
+int b200_device_can_access_peer(int dev, int peer, int* out) {
+  B200_CUDA_OK(cudaDeviceCanAccessPeer(out, dev, peer));
+  return 0;
+}
+
+}  // extern "C"
+
+// ===========================================================================
+// Device kernels
+// ===========================================================================
+namespace {
+
+// ---- barrier ---------------------------------------------------------------
+__global__ void comm_barrier_kernel(CommDev c, size_t flag_off, unsigned* seq_ctr) {
+  const int p = threadIdx.x;
+  const unsigned seq = *seq_ctr + 1u;
+  __syncwarp();
+  __threadfence_system();
+  if (p < c.world) {
+    st_release_sys_u32(peer_ptr<unsigned>(c, p, flag_off) + c.rank, seq);
+    wait_flag_ge(peer_ptr<unsigned>(c, c.rank, flag_off) + p, seq, c, p, 1u);
+  }
+  __syncwarp();
+  if (p == 0) *seq_ctr = seq;
+}
+
+// ---- broadcast (pull from root) ----------------------------------------------
+// flags: [0..world) "root ready" (written by root into every rank), [world..2*world)
+// "rank done" (written by every rank into root).
+__global__ void __launch_bounds__(256)
+comm_broadcast_kernel(CommDev c, int root, size_t buf_off, size_t nvec, size_t flag_off,
+                      unsigned* seq_ctr, unsigned* arrive_ctr) {
+  const unsigned seq = *seq_ctr + 1u;
+  unsigned* my_flags = peer_ptr<unsigned>(c, c.rank, flag_off);
+  if (c.rank == root) {
+    if (blockIdx.x == 0) {
+      __threadfence_system();
+      if (threadIdx.x < c.world && threadIdx.x != root)
+        st_release_sys_u32(peer_ptr<unsigned>(c, threadIdx.x, flag_off) + root, seq);
+      // root must not overwrite the buffer before every rank has copied it
+      if (threadIdx.x < c.world && threadIdx.x != root)
+        wait_flag_ge(my_flags + c.world + threadIdx.x, seq, c, threadIdx.x, 2u);
+    }
+  } else {
+    if (threadIdx.x == 0) wait_flag_ge(my_flags + root, seq, c, root, 3u);
+    __syncthreads();
+    const uint4* src = peer_ptr<uint4>(c, root, buf_off);
+    uint4* dst = peer_ptr<uint4>(c, c.rank, buf_off);
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec;
+         i += (size_t)gridDim.x * blockDim.x)
+      dst[i] = ld_volatile_u4(src + i);
+  }
+  // last CTA: publish completion, advance the sequence
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned prev = atomicAdd(arrive_ctr, 1u);
+    if (prev == gridDim.x - 1) {
+      *arrive_ctr = 0u;
+      if (c.rank != root)
+        st_release_sys_u32(peer_ptr<unsigned>(c, root, flag_off) + c.world + c.rank, seq);
+      *seq_ctr = seq;
+    }
+  }
+}
+
+// ---- send / recv mailbox -------------------------------------------------------
+// Per (dst <- src) pair: a mailbox of `box_bytes` in dst's arena and two counters:
+// flags[src] in dst's arena = chunks written so far, acks[dst] in src's arena = chunks
+// consumed so far. Counters persist across calls in seq_ctr[peer] (local device memory).
+__global__ void __launch_bounds__(1024)
+comm_send_kernel(CommDev c, int dst, const uint4* __restrict__ payload, size_t nvec,
+                 size_t box_off, size_t box_vec, size_t flag_off, size_t ack_off,
+                 unsigned* sent_ctr) {
+  __shared__ unsigned s_ok;
+  unsigned sent = sent_ctr[dst];
+  uint4* box = peer_ptr<uint4>(c, dst, box_off) + (size_t)c.rank * box_vec;
+  for (size_t done = 0; done < nvec; done += box_vec) {
+    if (threadIdx.x == 0)  // wait until the receiver has drained the previous chunk
+      s_ok = wait_flag_ge(peer_ptr<unsigned>(c, c.rank, ack_off) + dst, sent, c, dst, 4u);
+    __syncthreads();
+    const size_t m = min(box_vec, nvec - done);
+    for (size_t i = threadIdx.x; i < m; i += blockDim.x) box[i] = payload[done + i];
+    __threadfence_system();
+    __syncthreads();
+    ++sent;
+    if (threadIdx.x == 0)
+      st_release_sys_u32(peer_ptr<unsigned>(c, dst, flag_off) + c.rank, sent);
+  }
+  (void)s_ok;
+  if (threadIdx.x == 0) sent_ctr[dst] = sent;
+}
+
+__global__ void __launch_bounds__(1024)
+comm_recv_kernel(CommDev c, int src, uint4* __restrict__ out, size_t nvec, size_t box_off,
+                 size_t box_vec, size_t flag_off, size_t ack_off, unsigned* recv_ctr) {
+  unsigned got = recv_ctr[src];
+  const uint4* box = peer_ptr<uint4>(c, c.rank, box_off) + (size_t)src * box_vec;
+  for (size_t done = 0; done < nvec; done += box_vec) {
+    ++got;
+    if (threadIdx.x == 0)
+      wait_flag_ge(peer_ptr<unsigned>(c, c.rank, flag_off) + src, got, c, src, 5u);
+    __syncthreads();
+    const size_t m = min(box_vec, nvec - done);
+    for (size_t i = threadIdx.x; i < m; i += blockDim.x) out[done + i] = ld_volatile_u4(box + i);
+    __syncthreads();
+    if (threadIdx.x == 0)
+      st_release_sys_u32(peer_ptr<unsigned>(c, src, ack_off) + c.rank, got);
+  }
+  if (threadIdx.x == 0) recv_ctr[src] = got;
+}
+
+// ---- Net kernel B, multi-GPU ---------------------------------------------------
+// CTA b owns float4 columns [32b, 32b+32) of the flat gradient. It (1) sums the G local
+// partial rows, (2) pushes its 512-byte slice into every rank's staging slot
+// [seq&1][my rank], (3) raises flag [b][my rank] on every rank, (4) waits for the world's
+// flags for slice b, (5) sums the slices in rank order (bit-identical on every rank, so
+// replicas never diverge), scales by 1/world and applies SGD-momentum to its own replica.
+// No grid-wide or rank-wide barrier: CTA b only ever waits for CTA b of the other ranks.
+__global__ void __launch_bounds__(256)
+net_reduce_allreduce_sgd_kernel(CommDev c, const float* __restrict__ partial, int G,
+                                float* __restrict__ params, float* __restrict__ mom,
+                                float* __restrict__ grad_out, const float* __restrict__ hp,
+                                const float* __restrict__ loss_partial,
+                                float* __restrict__ loss_ring, int ring,
+                                unsigned long long* ctl, size_t stage_off, size_t flag_off,
+                                unsigned* seq_ctr, unsigned* arrive_ctr) {
+  __shared__ float4 sm[8][32];
+  constexpr int N4 = FLAT_SZ / 4;
+  const int cidx = threadIdx.x & 31, rg = threadIdx.x >> 5;
+  const int col = blockIdx.x * 32 + cidx;
+  const bool valid = col < N4;
+  const unsigned seq = *seq_ctr + 1u;  // every CTA reads it before the last one bumps it
+  const unsigned slot = seq & 1u;
+  const float4 s = sum_partial_rows_256(partial, G, FLAT_SZ, col, valid, sm);
+  __syncthreads();
+  if (rg == 0) sm[0][cidx] = s;
+  __syncthreads();
+  if (rg < c.world && valid) {
+    float4* dst = peer_ptr<float4>(c, rg, stage_off) +
+                  ((size_t)slot * c.world + c.rank) * N4 + col;
+    *dst = sm[0][cidx];
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x < c.world) {
+    const int p = threadIdx.x;
+    st_release_sys_u32(peer_ptr<unsigned>(c, p, flag_off) + blockIdx.x * B200_MAX_WORLD + c.rank,
+                       seq);
+    wait_flag_ge(peer_ptr<unsigned>(c, c.rank, flag_off) + blockIdx.x * B200_MAX_WORLD + p, seq,
+                 c, p, 6u);
+  }
+  __syncthreads();
+  if (rg == 0 && valid) {
+    const float4* st = peer_ptr<float4>(c, c.rank, stage_off) + (size_t)slot * c.world * N4 + col;
+    float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int r = 0; r < c.world; ++r) {
+      const float4 v = __ldcg(st + (size_t)r * N4);
+      g.x += v.x; g.y += v.y; g.z += v.z; g.w += v.w;
+    }
+    const float inv = 1.0f / (float)c.world;
+    g.x *= inv; g.y *= inv; g.z *= inv; g.w *= inv;
+    if (grad_out) reinterpret_cast<float4*>(grad_out)[col] = g;
+    if (params) {
+      const float lr = hp[0], mu = hp[1];
+      float4 pv = reinterpret_cast<float4*>(params)[col];
+      float4 bv = reinterpret_cast<float4*>(mom)[col];
+      bv.x = mu * bv.x + g.x; bv.y = mu * bv.y + g.y; bv.z = mu * bv.z + g.z; bv.w = mu * bv.w + g.w;
+      pv.x -= lr * bv.x; pv.y -= lr * bv.y; pv.z -= lr * bv.z; pv.w -= lr * bv.w;
+      reinterpret_cast<float4*>(params)[col] = pv;
+      reinterpret_cast<float4*>(mom)[col] = bv;
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned prev = atomicAdd(arrive_ctr, 1u);
+    if (prev == gridDim.x - 1) {
+      *arrive_ctr = 0u;
+      *seq_ctr = seq;
+      float l = 0.0f;
+      for (int r = 0; r < G; ++r) l += loss_partial[r];
+      const unsigned long long step = ctl[0];
+      if (loss_ring) loss_ring[step % (unsigned long long)ring] = l;  // this rank's batch loss
+      ctl[0] = step + 1ull;
+    }
+  }
+}
+
+// ---- generic all-reduce --------------------------------------------------------
+struct AllreduceArgs {
+  const uint4* in;        // local input (gradient bucket), nvec 16-byte vectors
+  uint4* out_local;       // ALGO 0: local destination of the reduced vector (may alias in)
+  size_t out_off;         // ALGO 1: arena offset of the symmetric destination buffer
+  size_t nvec;
+  size_t stage_off;       // arena offset of staging [2][world][src_vec]
+  size_t src_vec;         // vectors reserved per source rank in one slot
+  size_t flag_off;        // arena offset of flags [2][gmax][B200_MAX_WORLD]
+  int gmax;
+  unsigned* seq_ctr;
+  unsigned* arrive_ctr;
+  float scale;            // applied to the sum (1/world for the DDP mean)
+  // fused SGD (UPDATE = 1): the reduced gradient never reaches memory
+  float* master;          // fp32 master weights of the elements this rank updates
+  float* mom;             // fp32 momentum of the same elements
+  const float* hp;        // {lr, momentum, weight_decay, nesterov}
+  size_t state_base;      // element index (in the bucket) that master[0]/mom[0] correspond to
+};
+
+template <typename T> struct Vec;
+template <> struct Vec<float> {
+  static constexpr int N = 4;
+  __device__ static void load(const uint4& u, float* f) {
+    f[0] = __uint_as_float(u.x); f[1] = __uint_as_float(u.y);
+    f[2] = __uint_as_float(u.z); f[3] = __uint_as_float(u.w);
+  }
+  __device__ static uint4 store(const float* f) {
+    return make_uint4(__float_as_uint(f[0]), __float_as_uint(f[1]), __float_as_uint(f[2]),
+                      __float_as_uint(f[3]));
+  }
+};
+template <> struct Vec<__nv_bfloat16> {
+  static constexpr int N = 8;
+  __device__ static void load(const uint4& u, float* f) {
+    const unsigned w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      f[2 * i] = __uint_as_float(w[i] << 16);
+      f[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+    }
+  }
+  __device__ static uint4 store(const float* f) {
+    unsigned w[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const __nv_bfloat162 h = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+      w[i] = *reinterpret_cast<const unsigned*>(&h);
+    }
+    return make_uint4(w[0], w[1], w[2], w[3]);
+  }
+};
+
+// Sum the `world` staged copies of vector v in rank order, scale, optionally apply SGD.
+// Returns the vector to publish: the averaged gradient (UPDATE 0) or the new weights.
+template <typename T, int UPDATE>
+__device__ __forceinline__ uint4 reduce_vec(const CommDev& c, const AllreduceArgs& a,
+                                            const uint4* stage_slot, size_t v_local,
+                                            size_t v_global) {
+  constexpr int N = Vec<T>::N;
+  float acc[N];
+#pragma unroll
+  for (int i = 0; i < N; ++i) acc[i] = 0.0f;
+  for (int r = 0; r < c.world; ++r) {
+    float f[N];
+    Vec<T>::load(__ldcg(stage_slot + (size_t)r * a.src_vec + v_local), f);
+#pragma unroll
+    for (int i = 0; i < N; ++i) acc[i] += f[i];
+  }
+#pragma unroll
+  for (int i = 0; i < N; ++i) acc[i] *= a.scale;
+  if (UPDATE) {
+    const float lr = a.hp[0], mu = a.hp[1], wd = a.hp[2];
+    const size_t e0 = v_global * N - a.state_base;
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+      float w = a.master[e0 + i];
+      const float g = acc[i] + wd * w;
+      const float b = mu * a.mom[e0 + i] + g;
+      a.mom[e0 + i] = b;
+      w -= lr * b;
+      a.master[e0 + i] = w;
+      acc[i] = w;
+    }
+  }
+  return Vec<T>::store(acc);
+}
+
+// ALGO 0 one-shot: every rank pushes its whole bucket to every rank, every rank reduces
+//         everything (latency-optimal for small buckets: one hop).
+// ALGO 1 two-shot: rank o owns slice o. Everyone pushes slice o to o (reduce-scatter),
+//         o reduces (+ SGD on its shard of master weights/momentum) and pushes the result
+//         to everyone's destination buffer (all-gather). Bandwidth-optimal; optimizer
+//         state is sharded across ranks for free.
+template <typename T, int ALGO, int UPDATE>
+__global__ void __launch_bounds__(256) allreduce_kernel(CommDev c, AllreduceArgs a) {
+  const unsigned seq = *a.seq_ctr + 1u;
+  const unsigned slot = seq & 1u;
+  const int b = blockIdx.x, G = gridDim.x, W = c.world;
+  const size_t slot_vec = (size_t)W * a.src_vec;
+  unsigned* my_flags = peer_ptr<unsigned>(c, c.rank, a.flag_off);
+  const size_t fidx1 = ((size_t)0 * a.gmax + b) * B200_MAX_WORLD;
+  const size_t fidx2 = ((size_t)1 * a.gmax + b) * B200_MAX_WORLD;
+
+  if (ALGO == 0) {
+    const size_t per = (a.nvec + G - 1) / G;
+    const size_t lo = (size_t)b * per, hi = min(a.nvec, lo + per);
+    for (size_t v = lo + threadIdx.x; v < hi; v += blockDim.x) {
+      const uint4 x = a.in[v];
+      for (int p = 0; p < W; ++p)
+        peer_ptr<uint4>(c, p, a.stage_off)[slot * slot_vec + (size_t)c.rank * a.src_vec + v] = x;
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x < W) {
+      const int p = threadIdx.x;
+      st_release_sys_u32(peer_ptr<unsigned>(c, p, a.flag_off) + fidx1 + c.rank, seq);
+      wait_flag_ge(my_flags + fidx1 + p, seq, c, p, 7u);
+    }
+    __syncthreads();
+    const uint4* st = peer_ptr<uint4>(c, c.rank, a.stage_off) + slot * slot_vec;
+    for (size_t v = lo + threadIdx.x; v < hi; v += blockDim.x)
+      a.out_local[v] = reduce_vec<T, UPDATE>(c, a, st, v, v);
+  } else {
+    const size_t sl = (a.nvec + W - 1) / W;       // vectors per owner slice
+    const size_t sub = (sl + G - 1) / G;          // vectors per CTA inside a slice
+    const size_t slo = (size_t)b * sub, shi = min(sl, slo + sub);
+    // reduce-scatter by pushes
+    for (int o = 0; o < W; ++o) {
+      const size_t base = (size_t)o * sl;
+      uint4* dst = peer_ptr<uint4>(c, o, a.stage_off) + slot * slot_vec + (size_t)c.rank * a.src_vec;
+      for (size_t v = slo + threadIdx.x; v < shi; v += blockDim.x)
+        if (base + v < a.nvec) dst[v] = a.in[base + v];
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x < W) {
+      const int p = threadIdx.x;
+      st_release_sys_u32(peer_ptr<unsigned>(c, p, a.flag_off) + fidx1 + c.rank, seq);
+      wait_flag_ge(my_flags + fidx1 + p, seq, c, p, 8u);
+    }
+    __syncthreads();
+    // reduce my slice (+ SGD on my shard), all-gather by pushes
+    const uint4* st = peer_ptr<uint4>(c, c.rank, a.stage_off) + slot * slot_vec;
+    const size_t mybase = (size_t)c.rank * sl;
+    for (size_t v = slo + threadIdx.x; v < shi; v += blockDim.x) {
+      if (mybase + v >= a.nvec) break;
+      const uint4 r = reduce_vec<T, UPDATE>(c, a, st, v, mybase + v);
+      for (int p = 0; p < W; ++p) peer_ptr<uint4>(c, p, a.out_off)[mybase + v] = r;
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x < W) {
+      const int p = threadIdx.x;
+      st_release_sys_u32(peer_ptr<unsigned>(c, p, a.flag_off) + fidx2 + c.rank, seq);
+      wait_flag_ge(my_flags + fidx2 + p, seq, c, p, 9u);
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned prev = atomicAdd(a.arrive_ctr, 1u);
+    if (prev == gridDim.x - 1) {
+      *a.arrive_ctr = 0u;
+      *a.seq_ctr = seq;
+    }
+  }
+}
+
+}  // namespace
+
+// ===========================================================================
+// C ABI: launches
+// ===========================================================================
+extern "C" {
+
+struct B200CommHost {  // mirrors CommDev; filled by Python through b200_comm_make
+  CommDev dev;
+};
+
+int b200_comm_struct_size(void) { return (int)sizeof(CommDev); }
+
+// Fill a caller-provided CommDev blob (host memory, b200_comm_struct_size() bytes).
+int b200_comm_make(void* blob, int rank, int world, void* const* bases, unsigned* err,
+                   unsigned long long timeout_ns) {
+  B200_REQUIRE(world >= 1 && world <= B200_MAX_WORLD, "b200_comm_make: world %d not in [1,%d]",
+               world, B200_MAX_WORLD);
+  B200_REQUIRE(rank >= 0 && rank < world, "b200_comm_make: bad rank %d", rank);
+  CommDev c;
+  memset(&c, 0, sizeof(c));
+  c.rank = rank;
+  c.world = world;
+  for (int i = 0; i < world; ++i) c.base[i] = (char*)bases[i];
+  c.err = err;
+  c.timeout_ns = timeout_ns;
+  memcpy(blob, &c, sizeof(c));
+  return 0;
+}
+
+int b200_comm_barrier(const void* comm, size_t flag_off, unsigned* seq_ctr, void* stream) {
+  const CommDev& c = *(const CommDev*)comm;
+  comm_barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(c, flag_off, seq_ctr);
+  B200_LAUNCH_OK();
+  return 0;
+}
+
+int b200_comm_broadcast(const void* comm, int root, size_t buf_off, size_t bytes, size_t flag_off,
+                        unsigned* seq_ctr, unsigned* arrive_ctr, void* stream) {
+  const CommDev& c = *(const CommDev*)comm;
+  B200_REQUIRE(bytes % 16 == 0 && buf_off % 16 == 0, "b200_comm_broadcast: 16-byte alignment");
+  B200_REQUIRE(root >= 0 && root < c.world, "b200_comm_broadcast: bad root");
+  const size_t nvec = bytes / 16;
+  int blocks = (int)((nvec + 255) / 256);
+  if (blocks > 148 * 2) blocks = 148 * 2;
+  if (blocks < 1) blocks = 1;
+  comm_broadcast_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(c, root, buf_off, nvec, flag_off,
+                                                                  seq_ctr, arrive_ctr);
+  B200_LAUNCH_OK();
+  return 0;
+}
+
+int b200_comm_send(const void* comm, int dst, const void* payload, size_t bytes, size_t box_off,
+                   size_t box_bytes, size_t flag_off, size_t ack_off, unsigned* sent_ctr,
+                   void* stream) {
+  const CommDev& c = *(const CommDev*)comm;
+  B200_REQUIRE(dst >= 0 && dst < c.world && dst != c.rank, "b200_comm_send: bad destination %d", dst);
+  B200_REQUIRE(bytes > 0 && bytes % 16 == 0 && box_bytes % 16 == 0, "b200_comm_send: 16-byte granularity");
+  comm_send_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(c, dst, (const uint4*)payload, bytes / 16,
+                                                         box_off, box_bytes / 16, flag_off, ack_off,
+                                                         sent_ctr);
+  B200_LAUNCH_OK();
+  return 0;
+}
+
+int b200_comm_recv(const void* comm, int src, void* out, size_t bytes, size_t box_off,
+                   size_t box_bytes, size_t flag_off, size_t ack_off, unsigned* recv_ctr,
+                   void* stream) {
+  const CommDev& c = *(const CommDev*)comm;
+  B200_REQUIRE(src >= 0 && src < c.world && src != c.rank, "b200_comm_recv: bad source %d", src);
+  B200_REQUIRE(bytes > 0 && bytes % 16 == 0 && box_bytes % 16 == 0, "b200_comm_recv: 16-byte granularity");
+  comm_recv_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(c, src, (uint4*)out, bytes / 16, box_off,
+                                                         box_bytes / 16, flag_off, ack_off,
+                                                         recv_ctr);
+  B200_LAUNCH_OK();
+  return 0;
+}
+
+// Bytes of staging and flags the Net kernel B needs in the arena.
+size_t b200_comm_net_stage_bytes(void) { return (size_t)2 * B200_MAX_WORLD * FLAT_SZ * 4; }
+size_t b200_comm_net_flag_bytes(void) {
+  return (size_t)((FLAT_SZ / 4 + 31) / 32) * B200_MAX_WORLD * 4;
+}
+
+int b200_comm_net_reduce_allreduce_sgd(const void* comm, const float* partial, int rows,
+                                       float* params, float* mom, float* grad_out,
+                                       const float* hp, const float* loss_partial,
+                                       float* loss_ring, int ring, unsigned long long* ctl,
+                                       size_t stage_off, size_t flag_off, unsigned* seq_ctr,
+                                       unsigned* arrive_ctr, void* stream) {
+  const CommDev& c = *(const CommDev*)comm;
+  B200_REQUIRE(rows > 0 && rows <= 148, "b200_comm_net_reduce_allreduce_sgd: rows out of range");
+  const int blocks = (FLAT_SZ / 4 + 31) / 32;
+  net_reduce_allreduce_sgd_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(
+      c, partial, rows, params, mom, grad_out, hp, loss_partial, loss_ring, ring, ctl, stage_off,
+      flag_off, seq_ctr, arrive_ctr);
+  B200_LAUNCH_OK();
+  return 0;
+}
+
+// dtype: 0 fp32, 1 bf16. algo: 0 one-shot, 1 two-shot. update: 0 plain (mean/sum into the
+// destination), 1 fused SGD-momentum (destination receives the new weights).
+int b200_comm_allreduce(const void* comm, int dtype, int algo, int update, const void* in,
+                        void* out_local, size_t out_off, size_t bytes, size_t stage_off,
+                        size_t src_bytes, size_t flag_off, int gmax, unsigned* seq_ctr,
+                        unsigned* arrive_ctr, float scale, float* master, float* mom,
+                        const float* hp, size_t state_base, int blocks, void* stream) {
+  const CommDev& c = *(const CommDev*)comm;
+  B200_REQUIRE(bytes > 0 && bytes % 16 == 0, "b200_comm_allreduce: size must be a multiple of 16 B");
+  B200_REQUIRE(src_bytes % 16 == 0 && stage_off % 16 == 0 && out_off % 16 == 0,
+               "b200_comm_allreduce: 16-byte alignment");
+  AllreduceArgs a;
+  a.in = (const uint4*)in;
+  a.out_local = (uint4*)out_local;
+  a.out_off = out_off;
+  a.nvec = bytes / 16;
+  a.stage_off = stage_off;
+  a.src_vec = src_bytes / 16;
+  a.flag_off = flag_off;
+  a.gmax = gmax;
+  a.seq_ctr = seq_ctr;
+  a.arrive_ctr = arrive_ctr;
+  a.scale = scale;
+  a.master = master;
+  a.mom = mom;
+  a.hp = hp;
+  a.state_base = state_base;
+  const size_t need = (algo == 0) ? a.nvec : (a.nvec + c.world - 1) / c.world;
+  B200_REQUIRE(need <= a.src_vec, "b200_comm_allreduce: %zu B per source exceed the staging (%zu B)",
+               need * 16, src_bytes);
+  if (blocks <= 0) {
+    blocks = (int)((need + 1023) / 1024);  // ~16 KB per CTA
+    if (blocks > 128) blocks = 128;
+    if (blocks < 1) blocks = 1;
+  }
+  B200_REQUIRE(blocks <= gmax, "b200_comm_allreduce: %d CTAs exceed the flag table (%d)", blocks, gmax);
+  B200_REQUIRE(!update || (master && mom && hp), "b200_comm_allreduce: SGD fusion needs state");
+  cudaStream_t s = (cudaStream_t)stream;
+#define B200_AR(T, A, U) allreduce_kernel<T, A, U><<<blocks, 256, 0, s>>>(c, a)
+  if (dtype == 0) {
+    if (algo == 0) { if (update) B200_AR(float, 0, 1); else B200_AR(float, 0, 0); }
+    else           { if (update) B200_AR(float, 1, 1); else B200_AR(float, 1, 0); }
+  } else if (dtype == 1) {
+    if (algo == 0) { if (update) B200_AR(__nv_bfloat16, 0, 1); else B200_AR(__nv_bfloat16, 0, 0); }
+    else           { if (update) B200_AR(__nv_bfloat16, 1, 1); else B200_AR(__nv_bfloat16, 1, 0); }
+  } else {
+    B200_REQUIRE(false, "b200_comm_allreduce: unknown dtype %d", dtype);
+  }
+#undef B200_AR
+  B200_LAUNCH_OK();
+  return 0;
+}
+
+}  // extern "C"

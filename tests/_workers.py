@@ -1,0 +1,199 @@
+"""Rank entry points for the multi-process tests (must be importable for mp spawn)."""
+import os
+import sys
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parents[1]
+if str(ROOT) not in sys.path:
+    sys.path.insert(0, str(ROOT))
+
+import torch
+
+PKG = "csed_514_project_distributed_training_using_pytorch_b200"
+
+
+def _pg():
+    import importlib
+    return importlib.import_module(PKG + ".parallel")
+
+
+def p2p_demo(rank, world, backend, out_dir):
+    """The reference's run1.py/run2.py: rank 0 sends tensor(1.) to rank 1 (src/run1.py:8-17)."""
+    P = _pg()
+    comm = P.init_process_group(backend=backend, rank=rank, world_size=world)
+    t = torch.zeros(4, device=comm.device)
+    if rank == 0:
+        t += 1
+        P.send(t, dst=1)
+    elif rank == 1:
+        P.recv(t, src=0)
+    if comm.device.type == "cuda":
+        torch.cuda.synchronize()
+        comm.check_errors()
+    torch.save(t.cpu(), os.path.join(out_dir, f"p2p_{rank}.pt"))
+    P.destroy_process_group()
+
+
+def collectives(rank, world, backend, out_dir):
+    """barrier, broadcast, all_reduce (one-shot, two-shot; fp32, bf16), big send/recv."""
+    P = _pg()
+    comm = P.init_process_group(backend=backend, rank=rank, world_size=world)
+    dev = comm.device
+    res = {}
+    comm.barrier()
+    # broadcast of an arena tensor and of a plain tensor
+    a = comm.alloc(1000 * 4)
+    a.copy_(torch.arange(4000, dtype=torch.float32) * (rank + 1))
+    comm.broadcast(a, root=0)
+    b = torch.full((37,), float(rank), device=dev)
+    comm.broadcast(b, root=world - 1)
+    res["bc_arena"] = a.cpu()
+    res["bc_plain"] = b.cpu()
+    # all-reduce variants
+    for name, dtype in (("f32", torch.float32), ("bf16", torch.bfloat16)):
+        for algo in ("oneshot", "twoshot"):
+            for n in (8, 4096 + 8, 300000):
+                g = torch.Generator().manual_seed(100 + rank)
+                x = torch.randn(n, generator=g).to(dtype)
+                if backend == "gloo" and dtype == torch.bfloat16:
+                    continue
+                t = comm.alloc(n, dtype) if algo == "twoshot" else x.to(dev).clone()
+                t.copy_(x)
+                comm.all_reduce(t, op="mean", algo=algo)
+                res[f"ar_{name}_{algo}_{n}"] = t.float().cpu().clone()
+                # repeat on the same channel (slot reuse, sequence numbers)
+                t.copy_(x)
+                comm.all_reduce(t, op="sum", algo=algo)
+                res[f"ar2_{name}_{algo}_{n}"] = t.float().cpu().clone()
+    # multi-chunk send/recv ring: rank r -> r+1
+    if world >= 2:
+        n = (3 << 20) // 4 + 4  # > 1 MiB mailbox: exercises chunking + acks
+        src = torch.arange(n, dtype=torch.float32, device=dev) + rank
+        dst = torch.empty(n, dtype=torch.float32, device=dev)
+        nxt, prv = (rank + 1) % world, (rank - 1) % world
+        if backend == "gloo":
+            if rank % 2 == 0:
+                comm.send(src, nxt); comm.recv(dst, prv)
+            else:
+                comm.recv(dst, prv); comm.send(src, nxt)
+        else:
+            s2 = torch.cuda.Stream()
+            s2.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(s2):
+                comm.send(src, nxt)
+            comm.recv(dst, prv)
+            torch.cuda.current_stream().wait_stream(s2)
+        res["ring"] = dst[:8].cpu()
+        res["ring_ok"] = bool(torch.equal(dst.cpu(), torch.arange(n, dtype=torch.float32) + prv))
+    if dev.type == "cuda":
+        torch.cuda.synchronize()
+        comm.check_errors()
+    torch.save(res, os.path.join(out_dir, f"coll_{rank}.pt"))
+    P.destroy_process_group()
+
+
+def _small_mlp(seed):
+    torch.manual_seed(seed)
+    return torch.nn.Sequential(torch.nn.Linear(20, 64), torch.nn.ReLU(), torch.nn.Linear(64, 32),
+                               torch.nn.ReLU(), torch.nn.Linear(32, 5))
+
+
+def ddp_generic(rank, world, backend, out_dir, fuse, algo):
+    """DataParallel over an arbitrary nn.Module through autograd hooks (T2, T3, T4)."""
+    import importlib
+    P = _pg()
+    DP = importlib.import_module(PKG + ".parallel.data_parallel").DataParallel
+    SGD = importlib.import_module(PKG + ".ops.sgd").FlatSGD
+    comm = P.init_process_group(backend=backend, rank=rank, world_size=world)
+    dev = comm.device
+    model = _small_mlp(100 + rank).to(dev)       # ranks start DIFFERENT; DDP must sync them
+    # three buckets (one per Linear) so overlap / ordering is exercised
+    ddp = DP(model, comm, bucket_of=[2, 2, 1, 1, 0, 0],
+             fuse_sgd=(0.05, 0.5, 0.0) if fuse else None, algo=algo)
+    init = ddp.flat.param.clone().cpu()
+    opt = None if fuse else SGD(ddp.flat.param, ddp.flat.grad, lr=0.05, momentum=0.5)
+    losses = []
+    for step in range(4):
+        g = torch.Generator().manual_seed(1000 * step + rank)
+        x = torch.randn(8, 20, generator=g).to(dev)
+        y = torch.randint(0, 5, (8,), generator=g).to(dev)
+        ddp.zero_grad()
+        loss = torch.nn.functional.cross_entropy(ddp(x), y)
+        loss.backward()
+        if opt is not None:
+            if dev.type == "cuda":
+                torch.cuda.current_stream().wait_stream(ddp.reducer.stream)
+            opt.step()
+        losses.append(loss.item())
+    # eval forward under no_grad does no sync/bookkeeping (T4)
+    ddp.eval()
+    with torch.no_grad():
+        ddp(torch.zeros(2, 20, device=dev))
+    assert not ddp._pass_open
+    # no_sync: gradients stay local
+    ddp.train()
+    with ddp.no_sync():
+        ddp.zero_grad()
+        torch.nn.functional.cross_entropy(ddp(torch.full((2, 20), float(rank + 1), device=dev)),
+                                          torch.zeros(2, dtype=torch.long, device=dev)).backward()
+    local_grad = ddp.flat.grad.clone().cpu()
+    if dev.type == "cuda":
+        torch.cuda.current_stream().wait_stream(ddp.reducer.stream)
+        torch.cuda.synchronize()
+        comm.check_errors()
+    torch.save({"init": init, "final": ddp.flat.param.clone().cpu(), "losses": losses,
+                "local_grad": local_grad, "keys": list(ddp.state_dict().keys())},
+               os.path.join(out_dir, f"ddp_{rank}.pt"))
+    P.destroy_process_group()
+
+
+def net_ddp_fused(rank, world, backend, out_dir, use_graph):
+    """The reference's distributed loop body (src/train_dist.py:78-84) as two kernels."""
+    import importlib
+    P = _pg()
+    DP = importlib.import_module(PKG + ".parallel.data_parallel").DataParallel
+    Net = importlib.import_module(PKG + ".models").Net
+    oracle = importlib.import_module(PKG + ".models.oracle")
+    comm = P.init_process_group(backend=backend, rank=rank, world_size=world)
+    dev = comm.device
+    torch.manual_seed(1 + rank)
+    ddp = DP(Net().to(dev), comm)
+    init = ddp.flat.param.clone().cpu()
+    eng = ddp.fused_engine(lr=0.02, momentum=0.5)
+    B, steps = 16, 4
+    sx = torch.empty(B, 1, 28, 28, device=dev)
+    sy = torch.empty(B, dtype=torch.int64, device=dev)
+    m2 = torch.empty(B, 20, device=dev)
+    m3 = torch.empty(B, 50, device=dev)
+    graph = None
+    grads = []
+    for step in range(steps):
+        g = torch.Generator().manual_seed(1000 * step + rank)
+        x = torch.randn(B, 1, 28, 28, generator=g)
+        y = torch.randint(0, 10, (B,), generator=g)
+        a, b = oracle.make_masks(B, g)
+        sx.copy_(x); sy.copy_(y); m2.copy_(a); m3.copy_(b)
+        if use_graph:
+            if graph is None:
+                s = torch.cuda.Stream()
+                s.wait_stream(torch.cuda.current_stream())
+                with torch.cuda.stream(s):     # warm-up creates the comm regions
+                    snap = eng._snapshot()
+                    eng.step(sx, sy, masks=(m2, m3))
+                    eng._restore(snap)
+                torch.cuda.current_stream().wait_stream(s)
+                torch.cuda.synchronize()
+                comm.host_barrier()
+                graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(graph, stream=s):
+                    eng.step(sx, sy, masks=(m2, m3))
+            graph.replay()
+        else:
+            eng.step(sx, sy, masks=(m2, m3), write_grad=True)
+            grads.append(eng.flat.grad.clone().cpu())
+    torch.cuda.synchronize()
+    comm.check_errors()
+    torch.save({"init": init, "final": eng.flat.param.clone().cpu(), "grads": grads,
+                "losses": eng.last_losses(steps), "steps": eng.steps_done()},
+               os.path.join(out_dir, f"net_{rank}.pt"))
+    P.destroy_process_group()
