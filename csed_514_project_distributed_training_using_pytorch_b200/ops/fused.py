@@ -68,7 +68,9 @@ class FusedNetEngine:
         # ctl[0] = optimizer step counter, ctl[1] = step at which the current epoch started
         self.step_ctr = torch.zeros(2, dtype=torch.int64, device=dev)
         self.ring = ring
-        self.loss_ring = torch.zeros(ring, dtype=torch.float32, device=dev)
+        # [0, ring): per-step losses; [ring]: always the latest step's loss (fixed address
+        # for a per-step device->host copy)
+        self.loss_ring = torch.zeros(ring + 1, dtype=torch.float32, device=dev)
         self.seed = int(seed) & 0xFFFFFFFFFFFFFFFF
         self.dropout = dropout
         self.sample_base = 0 if comm is None else comm.rank * (1 << 20)
@@ -177,6 +179,11 @@ class FusedNetEngine:
         n = min(n, done, self.ring)
         idx = [(done - n + i) % self.ring for i in range(n)]
         return self.loss_ring[idx].cpu()
+
+    @property
+    def last_loss(self) -> torch.Tensor:
+        """1-element device view holding the most recent step's loss."""
+        return self.loss_ring[self.ring:self.ring + 1]
 
     # -- evaluation (K19) ------------------------------------------------------
     def evaluate_batch(self, x, y, x_mode=X_F32, gidx=None, accumulate=False, logp_out=None,

@@ -41,6 +41,7 @@ N.register_sigs({
     "b200_comm_broadcast": [c_p, c_i, c_sz, c_sz, c_sz, c_p, c_p, c_p],
     "b200_comm_send": [c_p, c_i, c_p, c_sz, c_sz, c_sz, c_sz, c_sz, c_p, c_p],
     "b200_comm_recv": [c_p, c_i, c_p, c_sz, c_sz, c_sz, c_sz, c_sz, c_p, c_p],
+    "b200_comm_sendrecv": [c_p, c_i, c_p, c_sz, c_i, c_p, c_sz, c_sz, c_sz, c_sz, c_sz, c_p, c_p, c_p],
     "b200_comm_net_stage_bytes": [],
     "b200_comm_net_flag_bytes": [],
     "b200_comm_net_reduce_allreduce_sgd": [c_p, c_p, c_i, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_p,
@@ -131,6 +132,13 @@ class GlooComm(BaseComm):
     def recv(self, tensor, src):
         dist.recv(tensor, src=src, group=self.cpu_group)
         return tensor
+
+    def sendrecv(self, send_tensor, dst, recv_tensor, src):
+        reqs = [dist.isend(send_tensor, dst=dst, group=self.cpu_group),
+                dist.irecv(recv_tensor, src=src, group=self.cpu_group)]
+        for r in reqs:
+            r.wait()
+        return recv_tensor
 
 
 class PeerComm(BaseComm):
@@ -285,6 +293,22 @@ class PeerComm(BaseComm):
             tensor.copy_(buf[:tensor.numel() * tensor.element_size()].view(tensor.dtype)
                          .view(tensor.shape))
         return tensor
+
+    def sendrecv(self, send_tensor: torch.Tensor, dst: int, recv_tensor: torch.Tensor, src: int):
+        """Send to dst and receive from src in ONE launch (ring shift / pairwise swap).
+        Use this instead of a concurrent send + recv pair on two streams: two launches on
+        one GPU are not guaranteed to overlap, and the mailbox acks would deadlock."""
+        sbuf, sbytes = self._p2p_payload(send_tensor, copy_in=True)
+        rbuf, rbytes = self._p2p_payload(recv_tensor, copy_in=False)
+        N.check(self.lib.b200_comm_sendrecv(self._blob, dst, sbuf.data_ptr(), sbytes, src,
+                                            rbuf.data_ptr(), rbytes, self._box, self.box_bytes,
+                                            self._p2p_flags, self._p2p_acks, self._sent.data_ptr(),
+                                            self._recvd.data_ptr(), N.stream()),
+                "b200_comm_sendrecv")
+        if rbuf.data_ptr() != recv_tensor.data_ptr():
+            recv_tensor.copy_(rbuf[:recv_tensor.numel() * recv_tensor.element_size()]
+                              .view(recv_tensor.dtype).view(recv_tensor.shape))
+        return recv_tensor
 
     def _p2p_payload(self, tensor, copy_in):
         nbytes = tensor.numel() * tensor.element_size()

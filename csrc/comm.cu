@@ -130,16 +130,15 @@ comm_broadcast_kernel(CommDev c, int root, size_t buf_off, size_t nvec, size_t f
 // Per (dst <- src) pair: a mailbox of `box_bytes` in dst's arena and two counters:
 // flags[src] in dst's arena = chunks written so far, acks[dst] in src's arena = chunks
 // consumed so far. Counters persist across calls in seq_ctr[peer] (local device memory).
-__global__ void __launch_bounds__(1024)
-comm_send_kernel(CommDev c, int dst, const uint4* __restrict__ payload, size_t nvec,
-                 size_t box_off, size_t box_vec, size_t flag_off, size_t ack_off,
-                 unsigned* sent_ctr) {
-  __shared__ unsigned s_ok;
+__device__ __forceinline__ void send_body(const CommDev& c, int dst,
+                                          const uint4* __restrict__ payload, size_t nvec,
+                                          size_t box_off, size_t box_vec, size_t flag_off,
+                                          size_t ack_off, unsigned* sent_ctr) {
   unsigned sent = sent_ctr[dst];
   uint4* box = peer_ptr<uint4>(c, dst, box_off) + (size_t)c.rank * box_vec;
   for (size_t done = 0; done < nvec; done += box_vec) {
     if (threadIdx.x == 0)  // wait until the receiver has drained the previous chunk
-      s_ok = wait_flag_ge(peer_ptr<unsigned>(c, c.rank, ack_off) + dst, sent, c, dst, 4u);
+      wait_flag_ge(peer_ptr<unsigned>(c, c.rank, ack_off) + dst, sent, c, dst, 4u);
     __syncthreads();
     const size_t m = min(box_vec, nvec - done);
     for (size_t i = threadIdx.x; i < m; i += blockDim.x) box[i] = payload[done + i];
@@ -149,13 +148,13 @@ comm_send_kernel(CommDev c, int dst, const uint4* __restrict__ payload, size_t n
     if (threadIdx.x == 0)
       st_release_sys_u32(peer_ptr<unsigned>(c, dst, flag_off) + c.rank, sent);
   }
-  (void)s_ok;
+  __syncthreads();
   if (threadIdx.x == 0) sent_ctr[dst] = sent;
 }
 
-__global__ void __launch_bounds__(1024)
-comm_recv_kernel(CommDev c, int src, uint4* __restrict__ out, size_t nvec, size_t box_off,
-                 size_t box_vec, size_t flag_off, size_t ack_off, unsigned* recv_ctr) {
+__device__ __forceinline__ void recv_body(const CommDev& c, int src, uint4* __restrict__ out,
+                                          size_t nvec, size_t box_off, size_t box_vec,
+                                          size_t flag_off, size_t ack_off, unsigned* recv_ctr) {
   unsigned got = recv_ctr[src];
   const uint4* box = peer_ptr<uint4>(c, c.rank, box_off) + (size_t)src * box_vec;
   for (size_t done = 0; done < nvec; done += box_vec) {
@@ -169,7 +168,36 @@ comm_recv_kernel(CommDev c, int src, uint4* __restrict__ out, size_t nvec, size_
     if (threadIdx.x == 0)
       st_release_sys_u32(peer_ptr<unsigned>(c, src, ack_off) + c.rank, got);
   }
+  __syncthreads();
   if (threadIdx.x == 0) recv_ctr[src] = got;
+}
+
+__global__ void __launch_bounds__(1024)
+comm_send_kernel(CommDev c, int dst, const uint4* __restrict__ payload, size_t nvec,
+                 size_t box_off, size_t box_vec, size_t flag_off, size_t ack_off,
+                 unsigned* sent_ctr) {
+  send_body(c, dst, payload, nvec, box_off, box_vec, flag_off, ack_off, sent_ctr);
+}
+
+__global__ void __launch_bounds__(1024)
+comm_recv_kernel(CommDev c, int src, uint4* __restrict__ out, size_t nvec, size_t box_off,
+                 size_t box_vec, size_t flag_off, size_t ack_off, unsigned* recv_ctr) {
+  recv_body(c, src, out, nvec, box_off, box_vec, flag_off, ack_off, recv_ctr);
+}
+
+// A send and a receive that must make progress together (ring shifts, pairwise swaps):
+// CTA 0 sends, CTA 1 receives, inside ONE launch, so both are resident by construction.
+// Two separate launches on one GPU are not guaranteed to run concurrently, and a
+// multi-chunk exchange would then deadlock on the mailbox acks.
+__global__ void __launch_bounds__(1024)
+comm_sendrecv_kernel(CommDev c, int dst, const uint4* __restrict__ payload, size_t send_vec,
+                     int src, uint4* __restrict__ out, size_t recv_vec, size_t box_off,
+                     size_t box_vec, size_t flag_off, size_t ack_off, unsigned* sent_ctr,
+                     unsigned* recv_ctr) {
+  if (blockIdx.x == 0)
+    send_body(c, dst, payload, send_vec, box_off, box_vec, flag_off, ack_off, sent_ctr);
+  else
+    recv_body(c, src, out, recv_vec, box_off, box_vec, flag_off, ack_off, recv_ctr);
 }
 
 // ---- Net kernel B, multi-GPU ---------------------------------------------------
@@ -242,7 +270,10 @@ net_reduce_allreduce_sgd_kernel(CommDev c, const float* __restrict__ partial, in
       float l = 0.0f;
       for (int r = 0; r < G; ++r) l += loss_partial[r];
       const unsigned long long step = ctl[0];
-      if (loss_ring) loss_ring[step % (unsigned long long)ring] = l;  // this rank's batch loss
+      if (loss_ring) {  // this rank's batch loss; slot [ring] always holds the latest
+        loss_ring[step % (unsigned long long)ring] = l;
+        loss_ring[ring] = l;
+      }
       ctl[0] = step + 1ull;
     }
   }
@@ -490,6 +521,23 @@ int b200_comm_recv(const void* comm, int src, void* out, size_t bytes, size_t bo
   comm_recv_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(c, src, (uint4*)out, bytes / 16, box_off,
                                                          box_bytes / 16, flag_off, ack_off,
                                                          recv_ctr);
+  B200_LAUNCH_OK();
+  return 0;
+}
+
+int b200_comm_sendrecv(const void* comm, int dst, const void* payload, size_t send_bytes, int src,
+                       void* out, size_t recv_bytes, size_t box_off, size_t box_bytes,
+                       size_t flag_off, size_t ack_off, unsigned* sent_ctr, unsigned* recv_ctr,
+                       void* stream) {
+  const CommDev& c = *(const CommDev*)comm;
+  B200_REQUIRE(dst >= 0 && dst < c.world && dst != c.rank, "b200_comm_sendrecv: bad destination");
+  B200_REQUIRE(src >= 0 && src < c.world && src != c.rank, "b200_comm_sendrecv: bad source");
+  B200_REQUIRE(send_bytes > 0 && recv_bytes > 0 && send_bytes % 16 == 0 && recv_bytes % 16 == 0 &&
+                   box_bytes % 16 == 0,
+               "b200_comm_sendrecv: 16-byte granularity");
+  comm_sendrecv_kernel<<<2, 1024, 0, (cudaStream_t)stream>>>(
+      c, dst, (const uint4*)payload, send_bytes / 16, src, (uint4*)out, recv_bytes / 16, box_off,
+      box_bytes / 16, flag_off, ack_off, sent_ctr, recv_ctr);
   B200_LAUNCH_OK();
   return 0;
 }

@@ -600,7 +600,10 @@ net_reduce_sgd_kernel(const float* __restrict__ partial, int G, float* __restric
     float l = 0.0f;
     for (int r = 0; r < G; ++r) l += loss_partial[r];
     const unsigned long long step = step_ptr ? *step_ptr : 0ull;
-    if (loss_ring) loss_ring[step % (unsigned long long)ring] = l;
+    if (loss_ring) {  // slot [ring] always holds the latest step's loss
+      loss_ring[step % (unsigned long long)ring] = l;
+      loss_ring[ring] = l;
+    }
     if (step_ptr) *step_ptr = step + 1ull;
   }
 }

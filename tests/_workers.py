@@ -71,20 +71,17 @@ def collectives(rank, world, backend, out_dir):
         src = torch.arange(n, dtype=torch.float32, device=dev) + rank
         dst = torch.empty(n, dtype=torch.float32, device=dev)
         nxt, prv = (rank + 1) % world, (rank - 1) % world
-        if backend == "gloo":
-            if rank % 2 == 0:
-                comm.send(src, nxt); comm.recv(dst, prv)
-            else:
-                comm.recv(dst, prv); comm.send(src, nxt)
-        else:
-            s2 = torch.cuda.Stream()
-            s2.wait_stream(torch.cuda.current_stream())
-            with torch.cuda.stream(s2):
-                comm.send(src, nxt)
-            comm.recv(dst, prv)
-            torch.cuda.current_stream().wait_stream(s2)
+        comm.sendrecv(src, nxt, dst, prv)
         res["ring"] = dst[:8].cpu()
         res["ring_ok"] = bool(torch.equal(dst.cpu(), torch.arange(n, dtype=torch.float32) + prv))
+        # one-directional multi-chunk transfer 0 -> 1 (sender and receiver on different GPUs)
+        big = torch.arange(n, dtype=torch.float32, device=dev) * 2.0
+        if rank == 0:
+            comm.send(big, 1)
+        elif rank == 1:
+            got = torch.empty_like(big)
+            comm.recv(got, 0)
+            res["oneway_ok"] = bool(torch.equal(got, big))
     if dev.type == "cuda":
         torch.cuda.synchronize()
         comm.check_errors()

@@ -25,6 +25,7 @@ def _check_collectives(res, world, bf16=False):
         assert torch.equal(res[r]["bc_arena"], torch.arange(4000, dtype=torch.float32))
         assert torch.equal(res[r]["bc_plain"], torch.full((37,), float(world - 1)))
         assert res[r]["ring_ok"]
+    assert res[1]["oneway_ok"]
     names = ["f32"] + (["bf16"] if bf16 else [])
     for name in names:
         dtype = torch.float32 if name == "f32" else torch.bfloat16
