@@ -16,6 +16,17 @@
 
 using namespace net;
 
+// ---------------------------------------------------------------------------
+// Built-in scratch for b200_conv1_bwd_noalloc (see the entry point at the end of this
+// file). It lives in the library image: every GPU that loads the library carries these
+// bytes until the process exits. Layout: [0, 256) arrival counter, then one 264-float
+// partial row per image of the batch.
+// ---------------------------------------------------------------------------
+#define B200_NOALLOC_MAX_BATCH 128
+#define B200_NOALLOC_ROW_FLOATS 264
+#define B200_NOALLOC_SCRATCH_BYTES (256 + B200_NOALLOC_MAX_BATCH * B200_NOALLOC_ROW_FLOATS * 4)
+static __device__ __align__(256) unsigned char g_noalloc_scratch[B200_NOALLOC_SCRATCH_BYTES];
+
 namespace {
 
 __device__ __forceinline__ float normalize_u8(unsigned v) {
@@ -872,6 +883,81 @@ int b200_net_eval(const float* params, const void* x, int x_mode, const long lon
     eval_reduce_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(loss_img, pred_img, B, out2, accumulate);
     B200_LAUNCH_OK();
   }
+  return 0;
+}
+
+}  // extern "C"
+
+
+// ===========================================================================
+// Entry point that allocates nothing
+// ===========================================================================
+#include <mutex>
+
+namespace {
+std::mutex g_noalloc_mu;
+unsigned char* g_noalloc_dev_ptr[64] = {nullptr};  // per device: address of g_noalloc_scratch
+}  // namespace
+
+extern "C" {
+
+int b200_conv1_bwd_noalloc_max_batch(void) { return B200_NOALLOC_MAX_BATCH; }
+size_t b200_conv1_bwd_noalloc_scratch_bytes(void) { return (size_t)B200_NOALLOC_SCRATCH_BYTES; }
+
+// conv1 weight/bias gradient with NO workspace argument and no allocation of any kind.
+//
+// Who needs this: code that may not call cudaMalloc (or anything that allocates behind the
+// scenes, torch's caching allocator included) at the point where it needs the gradient:
+// a host thread whose memory budget was fixed up front, a plugin that is handed its
+// buffers and a stream and nothing else, or a latency-critical loop where an allocation
+// could synchronise the device. b200_conv1_bwd asks such callers for a scratch buffer and
+// a zeroed counter they have no way to obtain; this variant keeps both inside the library
+// in a fixed array (g_noalloc_scratch, 135,424 bytes per GPU) instead.
+//
+// Same inputs, outputs and arithmetic as b200_conv1_bwd; the caller still passes x, da1,
+// a1, pos1 and receives dw [10,1,5,5] and db [10].
+//
+// Limits and rules
+//  * B <= 128 images (b200_conv1_bwd_noalloc_max_batch()); larger batches are refused with
+//    an error, use b200_conv1_bwd with your own scratch or split the batch.
+//  * The FIRST call on each device looks up the array's device address
+//    (cudaGetSymbolAddress, with that device current). Make that first call outside any
+//    stream capture; later calls only enqueue a 4-byte memset and the kernel.
+//  * Every call on a device shares the one array, which still holds the previous call's
+//    partial rows. The arrival counter is cleared at the start of each call; the rows need
+//    no clearing because each call overwrites every row it later reads. Two calls that
+//    overlap on the GPU (different streams, no dependency between them) race on the array
+//    and both results are garbage: serialise them.
+int b200_conv1_bwd_noalloc(const float* x, const float* da1, const float* a1, const void* pos1,
+                           float* dw, float* db, int B, void* stream) {
+  B200_REQUIRE(B > 0, "b200_conv1_bwd_noalloc: empty batch");
+  B200_REQUIRE(B <= B200_NOALLOC_MAX_BATCH,
+               "b200_conv1_bwd_noalloc: batch %d exceeds the built-in scratch (max %d images); "
+               "use b200_conv1_bwd with caller-provided scratch or split the batch",
+               B, B200_NOALLOC_MAX_BATCH);
+  int dev = 0;
+  B200_CUDA_OK(cudaGetDevice(&dev));
+  B200_REQUIRE(dev >= 0 && dev < 64, "b200_conv1_bwd_noalloc: device index %d out of range", dev);
+  unsigned char* base = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (g_noalloc_dev_ptr[dev] == nullptr) {
+      // In host code `g_noalloc_scratch` is only a handle for the symbol; the address the
+      // kernel can use has to be asked for, once per device, with that device current.
+      unsigned char* p = nullptr;
+      B200_CUDA_OK(cudaGetSymbolAddress((void**)&p, g_noalloc_scratch));
+      B200_REQUIRE(p != nullptr, "b200_conv1_bwd_noalloc: symbol address lookup returned null");
+      g_noalloc_dev_ptr[dev] = p;
+    }
+    base = g_noalloc_dev_ptr[dev];
+  }
+  unsigned* counter = reinterpret_cast<unsigned*>(base);
+  float* scratch = reinterpret_cast<float*>(base + 256);
+  cudaStream_t s = (cudaStream_t)stream;
+  B200_CUDA_OK(cudaMemsetAsync(counter, 0, sizeof(unsigned), s));
+  conv1_bwd_kernel<<<grid_for(B, 148), NT, 0, s>>>(x, da1, a1, (const uint16_t*)pos1, dw, db,
+                                                   scratch, counter, B);
+  B200_LAUNCH_OK();
   return 0;
 }
 

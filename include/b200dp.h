@@ -40,6 +40,16 @@ int b200_conv1_fwd(const float* x, const float* w, const float* b, float* a1, vo
 /* K13 conv1 weight/bias gradient. scratch: >= rows*264 floats, counter: zeroed u32. */
 int b200_conv1_bwd(const float* x, const float* da1, const float* a1, const void* pos1, float* dw,
                    float* db, float* scratch, unsigned* counter, int B, void* stream);
+/* Same gradient as b200_conv1_bwd for callers that cannot allocate device memory: no
+ * scratch/counter arguments, the workspace is a fixed 135,424-byte array inside the library
+ * (per GPU, held until exit). No counterpart in the reference. B <= 128
+ * (b200_conv1_bwd_noalloc_max_batch()), larger batches are refused. The first call on a
+ * device resolves the array's address: make it before any stream capture. All calls on a
+ * device share the array: calls that overlap on the GPU race, serialise them. */
+int b200_conv1_bwd_noalloc(const float* x, const float* da1, const float* a1, const void* pos1,
+                           float* dw, float* db, int B, void* stream);
+int b200_conv1_bwd_noalloc_max_batch(void);
+size_t b200_conv1_bwd_noalloc_scratch_bytes(void);
 /* K3+K4+K5 conv2 + bias + Dropout2d + pool + ReLU. mask [B,20]; mask_mode 0 none, 1 generate
  * (Philox, written to mask), 2 use caller's. pos2: uint8 [B,20,4,4]. Ref: src/model.py:17 */
 int b200_conv2_fwd(const float* a1, const float* w, const float* b, float* mask, int mask_mode,
