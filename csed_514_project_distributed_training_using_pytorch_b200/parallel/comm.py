@@ -45,7 +45,7 @@ N.register_sigs({
     "b200_comm_net_stage_bytes": [],
     "b200_comm_net_flag_bytes": [],
     "b200_comm_net_reduce_allreduce_sgd": [c_p, c_p, c_i, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_p,
-                                           c_sz, c_sz, c_p, c_p, c_p],
+                                           c_sz, c_sz, c_p, c_p, c_i, c_p],
     "b200_comm_allreduce": [c_p, c_i, c_i, c_i, c_p, c_p, c_sz, c_sz, c_sz, c_sz, c_sz, c_i, c_p,
                             c_p, c_f, c_p, c_p, c_p, c_sz, c_i, c_p],
 }, {"b200_comm_net_stage_bytes": c_sz, "b200_comm_net_flag_bytes": c_sz})
@@ -403,7 +403,8 @@ class PeerComm(BaseComm):
             N.ptr(eng.flat.momentum) if update else None,
             N.ptr(eng.flat.grad) if write_grad else None, N.ptr(eng.hp),
             N.ptr(eng.loss_partial), N.ptr(eng.loss_ring), eng.ring, N.ptr(eng.step_ctr),
-            n["stage"], n["flags"], n["seq"], n["arrive"], N.stream()),
+            n["stage"], n["flags"], n["seq"], n["arrive"],
+            int(os.environ.get("B200DP_NET_PROTOCOL", "0")), N.stream()),
             "b200_comm_net_reduce_allreduce_sgd")
 
     def close(self):

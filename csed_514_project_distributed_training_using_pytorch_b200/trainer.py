@@ -88,6 +88,7 @@ class Trainer:
         self._graphs = {}
         self._perm_dev = None
         self.examples_seen = 0
+        self.native_runner = True   # host-streaming steps go through csrc/runner.cu
         if cfg.resume:
             self.resume(cfg.resume)
 
@@ -340,6 +341,17 @@ class Trainer:
         eng = self.engine
         if eng is None:
             raise RuntimeError("train_steps_from_host needs the fused CUDA engine")
+        if loss_out is None:
+            loss_out = torch.empty(steps, dtype=torch.float32).pin_memory()
+        if self.cfg.cuda_graph and self.native_runner:
+            # native loop (csrc/runner.cu): 3 staging slots, copy/compute overlap, no Python
+            key = ("runner", batch, hx.dtype)
+            r = self._graphs.get(key)
+            if r is None:
+                from .ops.runner import NativeRunner
+                r = self._graphs[key] = NativeRunner(eng, batch, hx.dtype)
+            r.run(hx, hy, steps, loss_out)
+            return loss_out
         mode = X_U8 if hx.dtype == torch.uint8 else X_F32
         key = ("host", batch, hx.dtype)
         st = self._graphs.get(key)
@@ -350,8 +362,6 @@ class Trainer:
             g = eng.capture(sx, sy, mode, batch=batch) if self.cfg.cuda_graph else None
             st = self._graphs[key] = (sx, sy, g)
         sx, sy, g = st
-        if loss_out is None:
-            loss_out = torch.empty(steps, dtype=torch.float32).pin_memory()
         last = eng.last_loss
         for i in range(steps):
             sx.copy_(hx[i * batch:(i + 1) * batch], non_blocking=True)

@@ -279,6 +279,99 @@ net_reduce_allreduce_sgd_kernel(CommDev c, const float* __restrict__ partial, in
   }
 }
 
+// Low-latency variant of the kernel above: every 16-byte store carries two payload floats
+// and two copies of the sequence number ({x, seq, y, seq}), so the data validates itself
+// (8-byte halves are written atomically). No fence, no separate flag, no second NVLink
+// traversal: the receiver polls the payload words until both tags match. This is the
+// protocol choice for the 87 KB Net bucket, where the exchange is pure latency.
+__global__ void __launch_bounds__(256)
+net_reduce_allreduce_sgd_ll_kernel(CommDev c, const float* __restrict__ partial, int G,
+                                   float* __restrict__ params, float* __restrict__ mom,
+                                   float* __restrict__ grad_out, const float* __restrict__ hp,
+                                   const float* __restrict__ loss_partial,
+                                   float* __restrict__ loss_ring, int ring,
+                                   unsigned long long* ctl, size_t stage_off,
+                                   unsigned* seq_ctr, unsigned* arrive_ctr) {
+  __shared__ float4 sm[8][32];
+  constexpr int N4 = FLAT_SZ / 4;
+  const int cidx = threadIdx.x & 31, rg = threadIdx.x >> 5;
+  const int col = blockIdx.x * 32 + cidx;
+  const bool valid = col < N4;
+  const unsigned seq = *seq_ctr + 1u;
+  const unsigned slot = seq & 1u;
+  const float4 s = sum_partial_rows_256(partial, G, FLAT_SZ, col, valid, sm);
+  __syncthreads();
+  if (rg == 0) sm[0][cidx] = s;
+  __syncthreads();
+  const float4 mine = sm[0][cidx];
+  __syncthreads();
+  if (rg < c.world && rg != c.rank && valid) {
+    uint4* dst = peer_ptr<uint4>(c, rg, stage_off) +
+                 (((size_t)slot * c.world + c.rank) * N4 + col) * 2;
+    st_volatile_u4(dst, make_uint4(__float_as_uint(mine.x), seq, __float_as_uint(mine.y), seq));
+    st_volatile_u4(dst + 1, make_uint4(__float_as_uint(mine.z), seq, __float_as_uint(mine.w), seq));
+  }
+  if (rg < c.world && valid) {
+    float4 v = mine;
+    if (rg != c.rank) {
+      const uint4* src = peer_ptr<uint4>(c, c.rank, stage_off) +
+                         (((size_t)slot * c.world + rg) * N4 + col) * 2;
+      uint4 a = ld_volatile_u4(src), b = ld_volatile_u4(src + 1);
+      if (!(a.y == seq && a.w == seq && b.y == seq && b.w == seq)) {
+        const unsigned long long t0 = globaltimer_ns();
+        unsigned polls = 0;
+        for (;;) {
+          a = ld_volatile_u4(src);
+          b = ld_volatile_u4(src + 1);
+          if (a.y == seq && a.w == seq && b.y == seq && b.w == seq) break;
+          if ((++polls & 1023u) == 0u && globaltimer_ns() - t0 > c.timeout_ns) {
+            if (atomicCAS(c.err, 0u, 1u) == 0u) { c.err[1] = (unsigned)rg; c.err[2] = 6u; c.err[3] = seq; }
+            break;
+          }
+        }
+      }
+      v = make_float4(__uint_as_float(a.x), __uint_as_float(a.z), __uint_as_float(b.x),
+                      __uint_as_float(b.z));
+    }
+    sm[rg][cidx] = v;
+  }
+  __syncthreads();
+  if (rg == 0 && valid) {
+    float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int r = 0; r < c.world; ++r) {
+      const float4 v = sm[r][cidx];
+      g.x += v.x; g.y += v.y; g.z += v.z; g.w += v.w;
+    }
+    const float inv = 1.0f / (float)c.world;
+    g.x *= inv; g.y *= inv; g.z *= inv; g.w *= inv;
+    if (grad_out) reinterpret_cast<float4*>(grad_out)[col] = g;
+    if (params) {
+      const float lr = hp[0], mu = hp[1];
+      float4 pv = reinterpret_cast<float4*>(params)[col];
+      float4 bv = reinterpret_cast<float4*>(mom)[col];
+      bv.x = mu * bv.x + g.x; bv.y = mu * bv.y + g.y; bv.z = mu * bv.z + g.z; bv.w = mu * bv.w + g.w;
+      pv.x -= lr * bv.x; pv.y -= lr * bv.y; pv.z -= lr * bv.z; pv.w -= lr * bv.w;
+      reinterpret_cast<float4*>(params)[col] = pv;
+      reinterpret_cast<float4*>(mom)[col] = bv;
+    }
+  }
+  if (threadIdx.x == 0) {
+    const unsigned prev = atomicAdd(arrive_ctr, 1u);
+    if (prev == gridDim.x - 1) {
+      *arrive_ctr = 0u;
+      *seq_ctr = seq;
+      float l = 0.0f;
+      for (int r = 0; r < G; ++r) l += loss_partial[r];
+      const unsigned long long step = ctl[0];
+      if (loss_ring) {
+        loss_ring[step % (unsigned long long)ring] = l;
+        loss_ring[ring] = l;
+      }
+      ctl[0] = step + 1ull;
+    }
+  }
+}
+
 // ---- generic all-reduce --------------------------------------------------------
 struct AllreduceArgs {
   const uint4* in;        // local input (gradient bucket), nvec 16-byte vectors
@@ -543,7 +636,7 @@ int b200_comm_sendrecv(const void* comm, int dst, const void* payload, size_t se
 }
 
 // Bytes of staging and flags the Net kernel B needs in the arena.
-size_t b200_comm_net_stage_bytes(void) { return (size_t)2 * B200_MAX_WORLD * FLAT_SZ * 4; }
+size_t b200_comm_net_stage_bytes(void) { return (size_t)2 * B200_MAX_WORLD * FLAT_SZ * 4 * 2; }
 size_t b200_comm_net_flag_bytes(void) {
   return (size_t)((FLAT_SZ / 4 + 31) / 32) * B200_MAX_WORLD * 4;
 }
@@ -553,13 +646,18 @@ int b200_comm_net_reduce_allreduce_sgd(const void* comm, const float* partial, i
                                        const float* hp, const float* loss_partial,
                                        float* loss_ring, int ring, unsigned long long* ctl,
                                        size_t stage_off, size_t flag_off, unsigned* seq_ctr,
-                                       unsigned* arrive_ctr, void* stream) {
+                                       unsigned* arrive_ctr, int protocol, void* stream) {
   const CommDev& c = *(const CommDev*)comm;
   B200_REQUIRE(rows > 0 && rows <= 148, "b200_comm_net_reduce_allreduce_sgd: rows out of range");
   const int blocks = (FLAT_SZ / 4 + 31) / 32;
-  net_reduce_allreduce_sgd_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(
-      c, partial, rows, params, mom, grad_out, hp, loss_partial, loss_ring, ring, ctl, stage_off,
-      flag_off, seq_ctr, arrive_ctr);
+  if (protocol == 0)   // low latency: tagged payload words
+    net_reduce_allreduce_sgd_ll_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(
+        c, partial, rows, params, mom, grad_out, hp, loss_partial, loss_ring, ring, ctl, stage_off,
+        seq_ctr, arrive_ctr);
+  else                 // payload, system fence, then a flag per CTA
+    net_reduce_allreduce_sgd_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(
+        c, partial, rows, params, mom, grad_out, hp, loss_partial, loss_ring, ring, ctl, stage_off,
+        flag_off, seq_ctr, arrive_ctr);
   B200_LAUNCH_OK();
   return 0;
 }

@@ -143,7 +143,8 @@ int b200_comm_net_reduce_allreduce_sgd(const void* comm, const float* partial, i
                                        const float* hp, const float* loss_partial,
                                        float* loss_ring, int ring, unsigned long long* ctl,
                                        size_t stage_off, size_t flag_off, unsigned* seq_ctr,
-                                       unsigned* arrive_ctr, void* stream);
+                                       unsigned* arrive_ctr, int protocol /* 0 LL, 1 flag */,
+                                       void* stream);
 /* Generic bucket all-reduce. dtype 0 fp32 / 1 bf16; algo 0 one-shot / 1 two-shot;
  * update 1 fuses sharded SGD-momentum (destination receives new weights). */
 int b200_comm_allreduce(const void* comm, int dtype, int algo, int update, const void* in,

@@ -1,0 +1,87 @@
+"""Multi-GPU microbenchmarks (run under torchrun): fused Net kernel B latency, generic
+all-reduce sweep vs NCCL. Device-timed with CUDA events, max over ranks."""
+import json, os, sys
+from pathlib import Path
+sys.path.insert(0, str(Path(__file__).resolve().parents[1]))
+import torch
+import torch.distributed as dist
+from csed_514_project_distributed_training_using_pytorch_b200 import parallel as P
+from csed_514_project_distributed_training_using_pytorch_b200.models import Net
+from csed_514_project_distributed_training_using_pytorch_b200.parallel.data_parallel import DataParallel
+
+
+def timed(comm, fn, iters, warm=10):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize(); comm.host_barrier()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(iters):
+        fn()
+    b.record()
+    torch.cuda.synchronize()
+    comm.check_errors()
+    return comm.max_over_ranks(a.elapsed_time(b) / iters * 1e3)
+
+
+def main():
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    comm = P.init_process_group("b200", rank=rank, world_size=world)
+    dev = comm.device
+    out = {"world": world}
+    what = sys.argv[1] if len(sys.argv) > 1 else "net"
+    if what in ("net", "all"):
+        torch.manual_seed(1)
+        ddp = DataParallel(Net().to(dev), comm)
+        eng = ddp.fused_engine(0.02, 0.5)
+        B = 64
+        x = torch.randn(B, 1, 28, 28, device=dev); y = torch.randint(0, 10, (B,), device=dev)
+        eng.step(x, y)
+        out["kernelA_eager_us"] = timed(comm, lambda: eng.forward_backward(x, y), 200)
+        out["kernelB_eager_us"] = timed(comm, lambda: eng.reduce_and_update(B), 200)
+        # graphs of B only / A only / A+B
+        def graph_of(fn):
+            s = torch.cuda.Stream(); s.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(s):
+                fn()
+            torch.cuda.current_stream().wait_stream(s); torch.cuda.synchronize(); comm.host_barrier()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=s):
+                fn()
+            return g
+        gB = graph_of(lambda: eng.reduce_and_update(B))
+        out["kernelB_graph_us"] = timed(comm, gB.replay, 1000)
+        gA = graph_of(lambda: eng.forward_backward(x, y))
+        out["kernelA_graph_us"] = timed(comm, gA.replay, 1000)
+        gAB = graph_of(lambda: eng.step(x, y))
+        out["step_graph_us"] = timed(comm, gAB.replay, 1000)
+        out["barrier_us"] = timed(comm, comm.barrier, 500)
+    if what in ("sweep", "all"):
+        sizes = [4 << 10, 16 << 10, 64 << 10, 256 << 10, 1 << 20, 4 << 20, 16 << 20, 64 << 20, 256 << 20]
+        rows = []
+        os.environ.setdefault("B200DP_AR_STAGE_MB", "36")
+        for nbytes in sizes:
+            n = nbytes // 4
+            row = {"bytes": nbytes}
+            iters = 200 if nbytes <= (1 << 20) else (50 if nbytes <= (16 << 20) else 10)
+            t = comm.alloc(n, torch.float32) if nbytes <= (64 << 20) else None
+            if t is not None:
+                t.normal_()
+                if nbytes <= (4 << 20):
+                    row["oneshot_us"] = timed(comm, lambda: comm.all_reduce(t, "sum", "oneshot"), iters)
+                row["twoshot_us"] = timed(comm, lambda: comm.all_reduce(t, "sum", "twoshot"), iters)
+            x = torch.randn(n, device=dev)
+            row["nccl_us"] = timed(comm, lambda: dist.all_reduce(x), iters)
+            for k in ("oneshot_us", "twoshot_us", "nccl_us"):
+                if k in row:   # bus bandwidth = 2(N-1)/N * S / t
+                    row[k.replace("_us", "_busGBs")] = 2 * (world - 1) / world * nbytes / (row[k] * 1e-6) / 1e9
+            rows.append(row)
+        out["sweep"] = rows
+    if rank == 0:
+        print(json.dumps(out, indent=1))
+    P.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -229,3 +229,25 @@ def test_sgd_kernel_matches_torch(cuda_device):
         dg.copy_(g)
         sgd.step()
     torch.testing.assert_close(dp.cpu(), ref_p.detach(), rtol=1e-6, atol=1e-6)
+
+
+def test_native_runner_matches_python_loop(cuda_device):
+    """csrc/runner.cu (3 staging slots, copy/compute overlap) == the Python step loop."""
+    from csed_514_project_distributed_training_using_pytorch_b200.trainer import Trainer
+    from csed_514_project_distributed_training_using_pytorch_b200.utils.config import TrainConfig
+    B, steps = 64, 20
+    g = torch.Generator().manual_seed(0)
+    hx = torch.randn(steps * B, 784, generator=g).pin_memory()
+    hy = torch.randint(0, 10, (steps * B,), generator=g).pin_memory()
+    out = []
+    for native in (True, False):
+        tr = Trainer(TrainConfig(learning_rate=0.02), distributed_style=True)
+        tr.native_runner = native
+        l1 = tr.train_steps_from_host(hx, hy, 12, B)
+        l2 = tr.train_steps_from_host(hx[12 * B:], hy[12 * B:], 8, B)   # second call: slots wrap
+        torch.cuda.synchronize()
+        out.append((tr.engine.flat.param.clone(), torch.cat([l1, l2]).clone(), tr.engine.steps_done()))
+    assert out[0][2] == out[1][2] == steps
+    assert torch.equal(out[0][0], out[1][0])
+    assert torch.equal(out[0][1], out[1][1])
+    assert (out[0][1] > 1.5).all() and (out[0][1] < 3.5).all()
