@@ -1,0 +1,466 @@
+// bf16 GEMM on the 5th-generation tensor cores, hand-written for sm_100a (SURVEY row 8.16,
+// BASELINE.json config 4: the 784-4096-4096-10 MLP).
+//
+//   C[M,N] = A * B^T (+ bias) (ReLU) (masked by relu_mask > 0),   fp32 accumulation
+//
+// One kernel covers the three products of a linear layer y = x W^T + b
+// (reference layers: nn.Linear in src/model.py:12-13, widened per BASELINE.json):
+//   forward  y  = x  W^T     A = x  [M,K] K-major,        B = W  [N,K] K-major
+//   dgrad    dx = dy W       A = dy [M,Kred] K-major,      B = W  [Kred,N] MN-major
+//   wgrad    dW = dy^T x     A = dy [Kred,M] MN-major,     B = x  [Kred,N] MN-major
+// so no operand is ever transposed in memory: the majorness goes into the TMA box shape,
+// the shared-memory matrix descriptor and two bits of the instruction descriptor.
+//
+// Structure (one 128 x BN output tile per CTA, 192 threads):
+//   warp 0      TMA producer: cp.async.bulk.tensor.2d into a STAGES-deep ring of
+//               128B-swizzled A/B tiles, completion on `full` mbarriers (expect_tx)
+//   warp 1      TMEM allocator + MMA issuer: one elected lane issues
+//               tcgen05.mma.cta_group::1.kind::f16 (M=128, N=BN, K=16) four times per
+//               64-wide K block; tcgen05.commit releases the smem stage (`empty`) and
+//               finally signals `tmem_full`
+//   warps 2..5  epilogue: tcgen05.ld 32x32b.x32 (each warp its own 32 TMEM lanes = 32 rows),
+//               bias / ReLU / ReLU-mask, bf16 or fp32 stores with edge masking
+// TMA zero-fills out-of-bounds reads, so M, N, K need no padding (only 16-byte row pitch).
+#include <cuda.h>
+#include <cuda_bf16.h>
+
+#include <cstring>
+#include <mutex>
+#include <unordered_map>
+
+#include "common.cuh"
+
+namespace {
+
+constexpr int BM = 128;
+constexpr int BK = 64;          // bf16 elements per K block = one 128-byte swizzle row
+constexpr int UMMA_K = 16;
+constexpr int GEMM_THREADS = 192;
+
+// ---------------------------------------------------------------------------
+// PTX wrappers
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
+               "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t}" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void fence_barrier_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, uint64_t* bar,
+                                            int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4}], [%2];" ::"r"(smem_u32(dst)),
+      "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
+}
+__device__ __forceinline__ void tcgen05_fence_before() {
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tcgen05_fence_after() {
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                   smem_u32(dst_smem)),
+               "r"(ncols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols)
+               : "memory");
+}
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,
+                                          uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
+                   smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
+      "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]),
+        "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]),
+        "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]),
+        "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]),
+        "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]),
+        "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]),
+        "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() {
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// Shared-memory matrix descriptor (cute::UMMA::SmemDescriptor bit layout), 128B swizzle.
+//   K-major tile  : rows x 128 B; 8-row groups 1024 B apart  -> LBO = 1 (unused), SBO = 1024 B
+//   MN-major tile : [K rows][64 MN elems = 128 B]; the next 64 MN elements live `lbo_bytes`
+//                   further (one TMA box later); 8-row K groups 1024 B apart -> SBO = 1024 B
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t lbo_bytes,
+                                                   uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;   // descriptor version for sm_100
+  d |= (uint64_t)2 << 61;   // SWIZZLE_128B
+  return d;
+}
+
+// Instruction descriptor (cute::UMMA::InstrDescriptor): bf16 x bf16 -> fp32.
+__host__ __device__ constexpr uint32_t make_idesc(int M, int N, int a_mn, int b_mn) {
+  return (1u << 4)                    // c_format  = F32
+         | (1u << 7)                  // a_format  = BF16
+         | (1u << 10)                 // b_format  = BF16
+         | ((uint32_t)a_mn << 15)     // a_major   (1 = MN-major)
+         | ((uint32_t)b_mn << 16)     // b_major
+         | ((uint32_t)(N >> 3) << 17) // n_dim
+         | ((uint32_t)(M >> 4) << 24);// m_dim
+}
+
+struct GemmParams {
+  int M, N, K;
+  void* C;
+  int ldc;               // elements
+  int c_fp32;            // 1: fp32 output, 0: bf16
+  const __nv_bfloat16* bias;       // [N] or null
+  int relu;
+  const __nv_bfloat16* relu_mask;  // [M, ld_mask] or null: output zeroed where mask <= 0
+  int ld_mask;
+};
+
+template <int BN, bool B_MN> struct Cfg {
+  static constexpr int A_BYTES = BM * BK * 2;   // 16 KB
+  // an MN-major B tile is made of whole 64-column boxes even when BN < 64
+  static constexpr int B_BYTES = ((B_MN && BN < 64) ? 64 : BN) * BK * 2;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int STAGES = (BN >= 128) ? 6 : 8;
+  static constexpr int SMEM = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+  static constexpr int TMEM_COLS = BN < 32 ? 32 : BN;
+};
+
+template <int BN, bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
+                         const __grid_constant__ CUtensorMap map_b, GemmParams p) {
+  using C = Cfg<BN, B_MN>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~(uintptr_t)1023);
+  uint8_t* tiles = smem;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + C::STAGES * C::STAGE_BYTES);
+  uint64_t* empty = full + C::STAGES;
+  uint64_t* tmem_full = empty + C::STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
+  const int num_kb = (p.K + BK - 1) / BK;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&map_a);
+    tma_prefetch_desc(&map_b);
+    for (int s = 0; s < C::STAGES; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 1);
+    }
+    mbar_init(tmem_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, C::TMEM_COLS);
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      for (int kb = 0; kb < num_kb; ++kb) {
+        const int s = kb % C::STAGES;
+        const uint32_t ph = (kb / C::STAGES) & 1;
+        mbar_wait(&empty[s], ph ^ 1);
+        uint8_t* a_dst = tiles + s * C::STAGE_BYTES;
+        uint8_t* b_dst = a_dst + C::A_BYTES;
+        mbar_expect_tx(&full[s], C::STAGE_BYTES);
+        const int k0 = kb * BK;
+        if (A_MN) {   // global [Kred][M]: two boxes of 64 M-columns x 64 K-rows
+          tma_load_2d(a_dst, &map_a, &full[s], m0, k0);
+          tma_load_2d(a_dst + BK * 128, &map_a, &full[s], m0 + 64, k0);
+        } else {      // global [M][K]: one box of 64 K-columns x 128 rows
+          tma_load_2d(a_dst, &map_a, &full[s], k0, m0);
+        }
+        if (B_MN) {
+#pragma unroll
+          for (int j = 0; j < (BN + 63) / 64; ++j)
+            tma_load_2d(b_dst + j * BK * 128, &map_b, &full[s], n0 + 64 * j, k0);
+        } else {
+          tma_load_2d(b_dst, &map_b, &full[s], k0, n0);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer =====
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc(BM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
+      for (int kb = 0; kb < num_kb; ++kb) {
+        const int s = kb % C::STAGES;
+        const uint32_t ph = (kb / C::STAGES) & 1;
+        mbar_wait(&full[s], ph);
+        tcgen05_fence_after();
+        const uint32_t a_addr = smem_u32(tiles + s * C::STAGE_BYTES);
+        const uint32_t b_addr = a_addr + C::A_BYTES;
+#pragma unroll
+        for (int k = 0; k < BK / UMMA_K; ++k) {
+          // K-major: step 16 elements = 32 B inside the swizzled 128 B row.
+          // MN-major: step 16 K-rows = 2048 B.
+          const uint64_t adesc = A_MN ? make_smem_desc(a_addr + k * UMMA_K * 128, BK * 128, 1024)
+                                      : make_smem_desc(a_addr + k * UMMA_K * 2, 16, 1024);
+          const uint64_t bdesc = B_MN ? make_smem_desc(b_addr + k * UMMA_K * 128, BK * 128, 1024)
+                                      : make_smem_desc(b_addr + k * UMMA_K * 2, 16, 1024);
+          umma_bf16(tmem_base, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+        }
+        umma_commit(&empty[s]);          // frees the smem stage once these MMAs retire
+      }
+      umma_commit(tmem_full);            // accumulator complete
+    }
+  } else {
+    // ===== epilogue: warps 2..5, TMEM lane group = warp % 4 =====
+    const int lg = warp & 3;
+    mbar_wait(tmem_full, 0);
+    tcgen05_fence_after();
+    const int row = m0 + lg * 32 + lane;
+    const bool row_ok = row < p.M;
+    constexpr int CHUNK = BN >= 32 ? 32 : 16;
+#pragma unroll 1
+    for (int c0 = 0; c0 < BN; c0 += CHUNK) {
+      uint32_t r[CHUNK];
+      const uint32_t taddr = tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)c0;
+      if constexpr (CHUNK == 32) tmem_ld32(taddr, r); else tmem_ld16(taddr, r);
+      tmem_ld_wait();
+      if (row_ok) {
+        const int col0 = n0 + c0;
+        float v[CHUNK];
+#pragma unroll
+        for (int j = 0; j < CHUNK; ++j) v[j] = __uint_as_float(r[j]);
+        if (p.bias) {
+#pragma unroll
+          for (int j = 0; j < CHUNK; ++j)
+            if (col0 + j < p.N) v[j] += __bfloat162float(p.bias[col0 + j]);
+        }
+        if (p.relu) {
+#pragma unroll
+          for (int j = 0; j < CHUNK; ++j) v[j] = fmaxf(v[j], 0.0f);
+        }
+        if (p.relu_mask) {
+          const __nv_bfloat16* mrow = p.relu_mask + (size_t)row * p.ld_mask + col0;
+          if (col0 + CHUNK <= p.N && (p.ld_mask % 8) == 0) {
+#pragma unroll
+            for (int j = 0; j < CHUNK; j += 8) {
+              const uint4 mv = *reinterpret_cast<const uint4*>(mrow + j);
+              const uint32_t w[4] = {mv.x, mv.y, mv.z, mv.w};
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                if (__uint_as_float(w[q] << 16) <= 0.0f) v[j + 2 * q] = 0.0f;
+                if (__uint_as_float(w[q] & 0xffff0000u) <= 0.0f) v[j + 2 * q + 1] = 0.0f;
+              }
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < CHUNK; ++j)
+              if (col0 + j < p.N && __bfloat162float(mrow[j]) <= 0.0f) v[j] = 0.0f;
+          }
+        }
+        if (p.c_fp32) {
+          float* crow = reinterpret_cast<float*>(p.C) + (size_t)row * p.ldc + col0;
+          if (col0 + CHUNK <= p.N && (p.ldc % 4) == 0) {
+#pragma unroll
+            for (int j = 0; j < CHUNK; j += 4)
+              *reinterpret_cast<float4*>(crow + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+          } else {
+#pragma unroll
+            for (int j = 0; j < CHUNK; ++j)
+              if (col0 + j < p.N) crow[j] = v[j];
+          }
+        } else {
+          __nv_bfloat16* crow = reinterpret_cast<__nv_bfloat16*>(p.C) + (size_t)row * p.ldc + col0;
+          if (col0 + CHUNK <= p.N && (p.ldc % 8) == 0) {
+#pragma unroll
+            for (int j = 0; j < CHUNK; j += 8) {
+              uint32_t w[4];
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                const __nv_bfloat162 h = __floats2bfloat162_rn(v[j + 2 * q], v[j + 2 * q + 1]);
+                w[q] = *reinterpret_cast<const uint32_t*>(&h);
+              }
+              *reinterpret_cast<uint4*>(crow + j) = make_uint4(w[0], w[1], w[2], w[3]);
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < CHUNK; ++j)
+              if (col0 + j < p.N) crow[j] = __float2bfloat16_rn(v[j]);
+          }
+        }
+      }
+    }
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tcgen05_fence_after();
+    tmem_dealloc(tmem_base, C::TMEM_COLS);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Host: TMA descriptors through the driver entry point (no link-time libcuda dependency,
+// so the library still loads on a machine without a driver)
+// ---------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+// 2-D bf16 tensor [rows][cols] (cols contiguous, `pitch` elements between rows);
+// box = box_cols x box_rows, 128B swizzle, zero fill outside.
+int make_map(CUtensorMap* m, const void* base, long long rows, long long cols, long long pitch,
+             int box_cols, int box_rows) {
+  EncodeTiledFn enc = get_encode();
+  B200_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled is not available from this driver");
+  B200_REQUIRE((pitch * 2) % 16 == 0, "gemm: row pitch must be a multiple of 16 bytes (%lld elements)", pitch);
+  B200_REQUIRE(((uintptr_t)base & 15) == 0, "gemm: operand base must be 16-byte aligned");
+  const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  const cuuint64_t strides[1] = {(cuuint64_t)pitch * 2};
+  const cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims,
+                         strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                         CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  B200_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with code %d", (int)r);
+  return 0;
+}
+
+template <int BN, bool A_MN, bool B_MN>
+int launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p, cudaStream_t s) {
+  using C = Cfg<BN, B_MN>;
+  auto kern = gemm_bf16_tcgen05_kernel<BN, A_MN, B_MN>;
+  static bool attr_done[64] = {false};
+  int dev = 0;
+  B200_CUDA_OK(cudaGetDevice(&dev));
+  if (!attr_done[dev & 63]) {
+    B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM));
+    attr_done[dev & 63] = true;
+  }
+  dim3 grid((p.N + BN - 1) / BN, (p.M + BM - 1) / BM);
+  kern<<<grid, GEMM_THREADS, C::SMEM, s>>>(ma, mb, p);
+  B200_LAUNCH_OK();
+  return 0;
+}
+
+template <int BN>
+int dispatch_major(int a_mn, int b_mn, const CUtensorMap& ma, const CUtensorMap& mb,
+                   const GemmParams& p, cudaStream_t s) {
+  if (!a_mn && !b_mn) return launch<BN, false, false>(ma, mb, p, s);
+  if (!a_mn && b_mn) return launch<BN, false, true>(ma, mb, p, s);
+  if (a_mn && b_mn) return launch<BN, true, true>(ma, mb, p, s);
+  return launch<BN, true, false>(ma, mb, p, s);
+}
+
+}  // namespace
+
+extern "C" {
+
+// C[M,N] = op(A) * op(B)^T with fp32 accumulation on tcgen05 tensor cores.
+//   a_mn = 0: A is [M][K] (lda = K pitch);   a_mn = 1: A is [K][M] (lda = M pitch)
+//   b_mn = 0: B is [N][K] (ldb = K pitch);   b_mn = 1: B is [K][N] (ldb = N pitch)
+//   C is [M][ldc], bf16 (c_fp32 = 0) or fp32 (c_fp32 = 1)
+//   bias: bf16 [N] or null; relu: clamp at 0; relu_mask: bf16 [M][ld_mask] or null, output is
+//   zeroed where the mask is <= 0 (ReLU backward fused into dgrad).
+// All pitches in elements; operand pitches must be multiples of 8 elements (16 bytes).
+int b200_gemm_bf16(const void* A, int a_mn, long long lda, const void* B, int b_mn, long long ldb,
+                   void* C, int c_fp32, long long ldc, int M, int N, int K, const void* bias,
+                   int relu, const void* relu_mask, long long ld_mask, void* stream) {
+  B200_REQUIRE(M > 0 && N > 0 && K > 0, "b200_gemm_bf16: empty problem");
+  const int BN = (N <= 16) ? 16 : (N <= 32 ? 32 : (N <= 64 ? 64 : 128));
+  CUtensorMap ma, mb;
+  int e;
+  if (a_mn) e = make_map(&ma, A, K, M, lda, 64, 64); else e = make_map(&ma, A, M, K, lda, 64, BM);
+  if (e) return e;
+  if (b_mn) e = make_map(&mb, B, K, N, ldb, 64, 64); else e = make_map(&mb, B, N, K, ldb, 64, BN);
+  if (e) return e;
+  GemmParams p;
+  p.M = M; p.N = N; p.K = K;
+  p.C = C; p.ldc = (int)ldc; p.c_fp32 = c_fp32;
+  p.bias = (const __nv_bfloat16*)bias;
+  p.relu = relu;
+  p.relu_mask = (const __nv_bfloat16*)relu_mask;
+  p.ld_mask = (int)ld_mask;
+  cudaStream_t s = (cudaStream_t)stream;
+  switch (BN) {
+    case 16: return dispatch_major<16>(a_mn, b_mn, ma, mb, p, s);
+    case 32: return dispatch_major<32>(a_mn, b_mn, ma, mb, p, s);
+    case 64: return dispatch_major<64>(a_mn, b_mn, ma, mb, p, s);
+    default: return dispatch_major<128>(a_mn, b_mn, ma, mb, p, s);
+  }
+}
+
+}  // extern "C"

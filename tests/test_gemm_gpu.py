@@ -1,0 +1,53 @@
+"""tcgen05 bf16 GEMM vs a plain PyTorch fp32 reference of the same product."""
+import pytest
+import torch
+
+from csed_514_project_distributed_training_using_pytorch_b200.ops import gemm
+
+pytestmark = pytest.mark.gpu
+
+
+def _ref(A, B, a_mn, b_mn):
+    a = A.float().t() if a_mn else A.float()
+    b = B.float() if b_mn else B.float().t()
+    return a @ b
+
+
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, True), (True, False)])
+@pytest.mark.parametrize("M,N,K", [(128, 128, 64), (256, 384, 512), (64, 4096, 784), (104, 200, 72),
+                                   (512, 16, 4096), (16, 1024, 520), (304, 136, 1000)])
+def test_gemm_all_majors(cuda_device, a_mn, b_mn, M, N, K):
+    g = torch.Generator().manual_seed(M * 7 + N * 3 + K)
+    A = torch.randn((K, M) if a_mn else (M, K), generator=g).to(torch.bfloat16).to(cuda_device)
+    B = torch.randn((K, N) if b_mn else (N, K), generator=g).to(torch.bfloat16).to(cuda_device)
+    want = _ref(A, B, a_mn, b_mn)
+    got32 = gemm.gemm_bf16(A, B, a_mn, b_mn, out_dtype=torch.float32)
+    torch.testing.assert_close(got32, want, rtol=2e-3, atol=2e-2 * (K ** 0.5) / 8)
+    got16 = gemm.gemm_bf16(A, B, a_mn, b_mn)
+    torch.testing.assert_close(got16.float(), want, rtol=1.6e-2, atol=2e-2 * (K ** 0.5) / 4)
+
+
+def test_gemm_epilogues(cuda_device):
+    g = torch.Generator().manual_seed(5)
+    M, N, K = 192, 320, 256
+    x = torch.randn(M, K, generator=g).to(torch.bfloat16).to(cuda_device)
+    W = (torch.randn(N, K, generator=g) / 16).to(torch.bfloat16).to(cuda_device)
+    b = torch.randn(N, generator=g).to(torch.bfloat16).to(cuda_device)
+    y = gemm.linear_fwd(x, W, b, relu=True)
+    want = torch.relu(x.float() @ W.float().t() + b.float())
+    torch.testing.assert_close(y.float(), want, rtol=1.6e-2, atol=3e-2)
+    # dgrad with the ReLU mask of the producing activation fused in
+    dy = torch.randn(M, N, generator=g).to(torch.bfloat16).to(cuda_device)
+    act = torch.randn(M, K, generator=g).to(torch.bfloat16).to(cuda_device)
+    dx = gemm.linear_dgrad(dy, W, relu_mask=act)
+    want_dx = (dy.float() @ W.float()) * (act.float() > 0)
+    torch.testing.assert_close(dx.float(), want_dx, rtol=1.6e-2, atol=5e-2)
+    # wgrad
+    dW = gemm.linear_wgrad(dy, x)
+    want_dW = dy.float().t() @ x.float()
+    torch.testing.assert_close(dW.float(), want_dW, rtol=1.6e-2, atol=0.15)
+    # output into a strided slice of a larger (flat-bucket-like) buffer, fp32
+    big = torch.zeros(N, K + 8, dtype=torch.float32, device=cuda_device)
+    gemm.gemm_bf16(dy, x, True, True, out=big[:, :K])
+    torch.testing.assert_close(big[:, :K], want_dW, rtol=2e-3, atol=2e-2)
+    assert torch.count_nonzero(big[:, K:]) == 0
