@@ -15,8 +15,6 @@ c_p, c_i, c_ll = C.c_void_p, C.c_int, C.c_longlong
 N.register_sigs({
     "b200_gemm_bf16": [c_p, c_i, c_ll, c_p, c_i, c_ll, c_p, c_i, c_ll, c_i, c_i, c_i, c_p, c_i,
                        c_p, c_ll, c_p],
-    "b200_softmax_nll_bf16": [c_p, c_i, c_p, c_p, c_p, c_i, c_i, c_p],
-    "b200_colsum_bf16": [c_p, c_ll, c_p, c_i, c_i, c_p],
 })
 
 

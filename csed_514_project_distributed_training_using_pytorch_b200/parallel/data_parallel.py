@@ -42,6 +42,9 @@ class DataParallel(nn.Module):
                 comm.broadcast(buf, root=broadcast_from)
         self.reducer = Reducer(self.flat, comm, bucket_of=bucket_of, fuse_sgd=fuse_sgd, algo=algo)
         self._params = list(module.parameters())
+        self._grad_views = self.flat.views(self.flat.grad)
+        if hasattr(module, "sink"):
+            module.sink = self       # native layers route their gradients through us
         self._require_backward_sync = True
         self._pass_open = False
         for i, p in enumerate(self._params):
@@ -79,6 +82,20 @@ class DataParallel(nn.Module):
             self.reducer.prepare_for_backward()
             self._pass_open = True
         return self.module(*args, **kwargs)
+
+    # -- gradient sink: layers that write dW/db straight into the bucket --------------
+    def view(self, i: int) -> torch.Tensor:
+        """Slot of parameter i inside the flat gradient bucket."""
+        return self._grad_views[i]
+
+    def ready(self, i: int):
+        """Parameter i's gradient is final in its slot (called from a layer's backward)."""
+        if not (self._require_backward_sync and self._pass_open):
+            return
+        self.reducer.mark_ready(i)
+        if self.reducer.core.all_done():
+            self.reducer.finalize_backward()
+            self._pass_open = False
 
     @contextlib.contextmanager
     def no_sync(self):
