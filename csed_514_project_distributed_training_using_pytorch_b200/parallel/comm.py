@@ -321,21 +321,28 @@ class PeerComm(BaseComm):
         return tmp, pad
 
     # -- generic all-reduce ----------------------------------------------------
-    GMAX = 128
+    GMAX = 256
 
-    def _ar_channel(self, src_bytes_needed: int):
-        if self._ar is None or self._ar["src_bytes"] < src_bytes_needed:
-            src_bytes = max(src_bytes_needed, int(os.environ.get("B200DP_AR_STAGE_MB", "4")) << 20)
-            src_bytes = (src_bytes + 255) // 256 * 256
-            self._ar = {
-                "src_bytes": src_bytes,
-                "stage": self._region(2 * self.world_size * src_bytes),
-                "flags": self._region(2 * self.GMAX * MAX_WORLD * 4),
-                "seq": self._counter(), "arrive": self._counter(),
-            }
+    def _ar_channel(self, algo: int, src_bytes_needed: int):
+        """Staging + flags of the generic all-reduce. The tagged-word (one-shot) and the bulk
+        (two-shot) protocols get SEPARATE staging: a stale bulk payload word must never be
+        mistaken for a sequence tag."""
+        if self._ar is None:
+            self._ar = {"flags": self._region(2 * self.GMAX * MAX_WORLD * 4),
+                        "seq": self._counter(), "arrive": self._counter(), "stages": {}}
             torch.cuda.synchronize(self.device)
             self.host_barrier()
-        return self._ar
+        st = self._ar["stages"].get(algo)
+        if st is None or st["src_bytes"] < src_bytes_needed:
+            floor_mb = "1" if algo == 0 else os.environ.get("B200DP_AR_STAGE_MB", "8")
+            src_bytes = max(src_bytes_needed, int(floor_mb) << 20)
+            src_bytes = (src_bytes + 255) // 256 * 256
+            st = self._ar["stages"][algo] = {
+                "src_bytes": src_bytes,
+                "stage": self._region(2 * self.world_size * src_bytes)}
+            torch.cuda.synchronize(self.device)
+            self.host_barrier()
+        return dict(self._ar, **st)
 
     def choose_algo(self, nbytes: int) -> int:
         """Measured crossover (profiles/allreduce_sweep.md): one-shot below, two-shot above."""
@@ -359,8 +366,8 @@ class PeerComm(BaseComm):
             if isinstance(algo, str) else int(algo)
         W = self.world_size
         nvec = nbytes // 16
-        need = nbytes if a == 0 else ((nvec + W - 1) // W) * 16
-        ch = self._ar_channel(need)
+        need = 2 * nbytes if a == 0 else ((nvec + W - 1) // W) * 16   # one-shot stages tagged words
+        ch = self._ar_channel(a, need)
         scale = 1.0 / W if op == "mean" else 1.0
         if sgd is None:
             out_t = tensor

@@ -47,6 +47,7 @@ class DataParallel(nn.Module):
             module.sink = self       # native layers route their gradients through us
         self._require_backward_sync = True
         self._pass_open = False
+        self._sunk = set()
         for i, p in enumerate(self._params):
             if p.requires_grad:
                 p.register_post_accumulate_grad_hook(self._make_hook(i))
@@ -62,6 +63,8 @@ class DataParallel(nn.Module):
         def hook(param):
             if not (self._require_backward_sync and self._pass_open):
                 return
+            if i in self._sunk:      # a native layer already delivered this gradient
+                return
             # autograd may have rebound .grad to a fresh tensor: move it into the bucket
             s = self.flat.slots[i]
             slot = self.flat.grad[s.offset:s.offset + s.numel].view(s.shape)
@@ -74,14 +77,23 @@ class DataParallel(nn.Module):
                 self._pass_open = False
         return hook
 
-    def forward(self, *args, **kwargs):
+    def _begin_pass(self):
         if torch.is_grad_enabled() and self.training and self._require_backward_sync:
             # make sure the previous step's (fused) update is visible to this forward
             if self.reducer.is_cuda:
                 torch.cuda.current_stream().wait_stream(self.reducer.stream)
             self.reducer.prepare_for_backward()
             self._pass_open = True
+            self._sunk = set()
+
+    def forward(self, *args, **kwargs):
+        self._begin_pass()
         return self.module(*args, **kwargs)
+
+    def loss(self, *args, **kwargs):
+        """module.loss(...) with the same backward bookkeeping as forward()."""
+        self._begin_pass()
+        return self.module.loss(*args, **kwargs)
 
     # -- gradient sink: layers that write dW/db straight into the bucket --------------
     def view(self, i: int) -> torch.Tensor:
@@ -92,6 +104,7 @@ class DataParallel(nn.Module):
         """Parameter i's gradient is final in its slot (called from a layer's backward)."""
         if not (self._require_backward_sync and self._pass_open):
             return
+        self._sunk.add(i)
         self.reducer.mark_ready(i)
         if self.reducer.core.all_done():
             self.reducer.finalize_backward()

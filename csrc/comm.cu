@@ -425,22 +425,11 @@ template <> struct Vec<__nv_bfloat16> {
   }
 };
 
-// Sum the `world` staged copies of vector v in rank order, scale, optionally apply SGD.
-// Returns the vector to publish: the averaged gradient (UPDATE 0) or the new weights.
+// Scale the rank-ordered sum, optionally apply SGD-momentum to the fp32 master weights, and
+// pack the vector to publish: the averaged gradient (UPDATE 0) or the new weights.
 template <typename T, int UPDATE>
-__device__ __forceinline__ uint4 reduce_vec(const CommDev& c, const AllreduceArgs& a,
-                                            const uint4* stage_slot, size_t v_local,
-                                            size_t v_global) {
+__device__ __forceinline__ uint4 finish_vec(const AllreduceArgs& a, float* acc, size_t v_global) {
   constexpr int N = Vec<T>::N;
-  float acc[N];
-#pragma unroll
-  for (int i = 0; i < N; ++i) acc[i] = 0.0f;
-  for (int r = 0; r < c.world; ++r) {
-    float f[N];
-    Vec<T>::load(__ldcg(stage_slot + (size_t)r * a.src_vec + v_local), f);
-#pragma unroll
-    for (int i = 0; i < N; ++i) acc[i] += f[i];
-  }
 #pragma unroll
   for (int i = 0; i < N; ++i) acc[i] *= a.scale;
   if (UPDATE) {
@@ -460,51 +449,96 @@ __device__ __forceinline__ uint4 reduce_vec(const CommDev& c, const AllreduceArg
   return Vec<T>::store(acc);
 }
 
-// ALGO 0 one-shot: every rank pushes its whole bucket to every rank, every rank reduces
-//         everything (latency-optimal for small buckets: one hop).
-// ALGO 1 two-shot: rank o owns slice o. Everyone pushes slice o to o (reduce-scatter),
-//         o reduces (+ SGD on its shard of master weights/momentum) and pushes the result
-//         to everyone's destination buffer (all-gather). Bandwidth-optimal; optimizer
-//         state is sharded across ranks for free.
+// Read one tagged (LL) vector: two 16-byte words {x, seq, y, seq} {z, seq, w, seq}; spin until
+// all four tags carry this call's sequence number (bounded).
+__device__ __forceinline__ uint4 ll_read(const uint4* src, unsigned seq, const CommDev& c,
+                                         int peer) {
+  uint4 a = ld_volatile_u4(src), b = ld_volatile_u4(src + 1);
+  if (!(a.y == seq && a.w == seq && b.y == seq && b.w == seq)) {
+    const unsigned long long t0 = globaltimer_ns();
+    unsigned polls = 0;
+    for (;;) {
+      a = ld_volatile_u4(src);
+      b = ld_volatile_u4(src + 1);
+      if (a.y == seq && a.w == seq && b.y == seq && b.w == seq) break;
+      if ((++polls & 1023u) == 0u && globaltimer_ns() - t0 > c.timeout_ns) {
+        if (atomicCAS(c.err, 0u, 1u) == 0u) { c.err[1] = (unsigned)peer; c.err[2] = 7u; c.err[3] = seq; }
+        break;
+      }
+    }
+  }
+  return make_uint4(a.x, a.z, b.x, b.z);
+}
+
+constexpr int AR_THREADS = 512;
+
+// ALGO 0 one-shot, low latency: every rank pushes its whole bucket to every rank as tagged
+//         words (payload + sequence number in each 8 bytes: no fence, no flag, one NVLink
+//         traversal) and every rank reduces everything. For small buckets.
+// ALGO 1 two-shot, bandwidth: rank o owns slice o. Everyone pushes slice o to o
+//         (reduce-scatter), o reduces (+ SGD on its shard of master weights/momentum) and
+//         pushes the result to everyone's destination buffer (all-gather). Optimizer state
+//         is sharded across ranks for free. Bulk copies keep 4 x 16 B in flight per thread.
 template <typename T, int ALGO, int UPDATE>
-__global__ void __launch_bounds__(256) allreduce_kernel(CommDev c, AllreduceArgs a) {
+__global__ void __launch_bounds__(AR_THREADS) allreduce_kernel(CommDev c, AllreduceArgs a) {
+  constexpr int N = Vec<T>::N;
   const unsigned seq = *a.seq_ctr + 1u;
   const unsigned slot = seq & 1u;
   const int b = blockIdx.x, G = gridDim.x, W = c.world;
+  const int nt = blockDim.x;
   const size_t slot_vec = (size_t)W * a.src_vec;
-  unsigned* my_flags = peer_ptr<unsigned>(c, c.rank, a.flag_off);
-  const size_t fidx1 = ((size_t)0 * a.gmax + b) * B200_MAX_WORLD;
-  const size_t fidx2 = ((size_t)1 * a.gmax + b) * B200_MAX_WORLD;
 
   if (ALGO == 0) {
     const size_t per = (a.nvec + G - 1) / G;
     const size_t lo = (size_t)b * per, hi = min(a.nvec, lo + per);
-    for (size_t v = lo + threadIdx.x; v < hi; v += blockDim.x) {
+    for (size_t v = lo + threadIdx.x; v < hi; v += nt) {
       const uint4 x = a.in[v];
-      for (int p = 0; p < W; ++p)
-        peer_ptr<uint4>(c, p, a.stage_off)[slot * slot_vec + (size_t)c.rank * a.src_vec + v] = x;
+      const uint4 w0 = make_uint4(x.x, seq, x.y, seq), w1 = make_uint4(x.z, seq, x.w, seq);
+      for (int p = 0; p < W; ++p) {
+        if (p == c.rank) continue;
+        uint4* dst = peer_ptr<uint4>(c, p, a.stage_off) + slot * slot_vec +
+                     (size_t)c.rank * a.src_vec + 2 * v;
+        st_volatile_u4(dst, w0);
+        st_volatile_u4(dst + 1, w1);
+      }
     }
-    __threadfence_system();
-    __syncthreads();
-    if (threadIdx.x < W) {
-      const int p = threadIdx.x;
-      st_release_sys_u32(peer_ptr<unsigned>(c, p, a.flag_off) + fidx1 + c.rank, seq);
-      wait_flag_ge(my_flags + fidx1 + p, seq, c, p, 7u);
-    }
-    __syncthreads();
     const uint4* st = peer_ptr<uint4>(c, c.rank, a.stage_off) + slot * slot_vec;
-    for (size_t v = lo + threadIdx.x; v < hi; v += blockDim.x)
-      a.out_local[v] = reduce_vec<T, UPDATE>(c, a, st, v, v);
+    for (size_t v = lo + threadIdx.x; v < hi; v += nt) {
+      float acc[N];
+#pragma unroll
+      for (int i = 0; i < N; ++i) acc[i] = 0.0f;
+      for (int r = 0; r < W; ++r) {
+        const uint4 x = (r == c.rank) ? a.in[v] : ll_read(st + (size_t)r * a.src_vec + 2 * v, seq, c, r);
+        float f[N];
+        Vec<T>::load(x, f);
+#pragma unroll
+        for (int i = 0; i < N; ++i) acc[i] += f[i];
+      }
+      a.out_local[v] = finish_vec<T, UPDATE>(a, acc, v);
+    }
   } else {
+    unsigned* my_flags = peer_ptr<unsigned>(c, c.rank, a.flag_off);
+    const size_t fidx1 = ((size_t)0 * a.gmax + b) * B200_MAX_WORLD;
+    const size_t fidx2 = ((size_t)1 * a.gmax + b) * B200_MAX_WORLD;
     const size_t sl = (a.nvec + W - 1) / W;       // vectors per owner slice
     const size_t sub = (sl + G - 1) / G;          // vectors per CTA inside a slice
     const size_t slo = (size_t)b * sub, shi = min(sl, slo + sub);
-    // reduce-scatter by pushes
-    for (int o = 0; o < W; ++o) {
+    // reduce-scatter by pushes: my sub-slice of owner o's slice goes to o's staging
+    for (int oo = 0; oo < W; ++oo) {
+      const int o = (c.rank + oo) % W;            // stagger destinations across ranks
       const size_t base = (size_t)o * sl;
+      const size_t lim = min(shi, a.nvec > base ? a.nvec - base : 0);
       uint4* dst = peer_ptr<uint4>(c, o, a.stage_off) + slot * slot_vec + (size_t)c.rank * a.src_vec;
-      for (size_t v = slo + threadIdx.x; v < shi; v += blockDim.x)
-        if (base + v < a.nvec) dst[v] = a.in[base + v];
+      const uint4* src = a.in + base;
+      for (size_t v = slo + threadIdx.x; v < lim; v += 4 * (size_t)nt) {
+        uint4 x[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          if (v + (size_t)u * nt < lim) x[u] = src[v + (size_t)u * nt];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          if (v + (size_t)u * nt < lim) dst[v + (size_t)u * nt] = x[u];
+      }
     }
     __threadfence_system();
     __syncthreads();
@@ -517,10 +551,34 @@ __global__ void __launch_bounds__(256) allreduce_kernel(CommDev c, AllreduceArgs
     // reduce my slice (+ SGD on my shard), all-gather by pushes
     const uint4* st = peer_ptr<uint4>(c, c.rank, a.stage_off) + slot * slot_vec;
     const size_t mybase = (size_t)c.rank * sl;
-    for (size_t v = slo + threadIdx.x; v < shi; v += blockDim.x) {
-      if (mybase + v >= a.nvec) break;
-      const uint4 r = reduce_vec<T, UPDATE>(c, a, st, v, mybase + v);
-      for (int p = 0; p < W; ++p) peer_ptr<uint4>(c, p, a.out_off)[mybase + v] = r;
+    const size_t mylim = min(shi, a.nvec > mybase ? a.nvec - mybase : 0);
+    for (size_t v = slo + threadIdx.x; v < mylim; v += 2 * (size_t)nt) {
+      uint4 res[2];
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const size_t vv = v + (size_t)u * nt;
+        if (vv < mylim) {
+          float acc[N];
+#pragma unroll
+          for (int i = 0; i < N; ++i) acc[i] = 0.0f;
+          for (int r = 0; r < W; ++r) {
+            float f[N];
+            Vec<T>::load(__ldcg(st + (size_t)r * a.src_vec + vv), f);
+#pragma unroll
+            for (int i = 0; i < N; ++i) acc[i] += f[i];
+          }
+          res[u] = finish_vec<T, UPDATE>(a, acc, mybase + vv);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const size_t vv = v + (size_t)u * nt;
+        if (vv < mylim)
+          for (int pp = 0; pp < W; ++pp) {
+            const int p = (c.rank + pp) % W;
+            peer_ptr<uint4>(c, p, a.out_off)[mybase + vv] = res[u];
+          }
+      }
     }
     __threadfence_system();
     __syncthreads();
@@ -689,18 +747,21 @@ int b200_comm_allreduce(const void* comm, int dtype, int algo, int update, const
   a.mom = mom;
   a.hp = hp;
   a.state_base = state_base;
-  const size_t need = (algo == 0) ? a.nvec : (a.nvec + c.world - 1) / c.world;
+  // one-shot stages tagged words (2x the payload); two-shot stages one slice per source
+  const size_t need = (algo == 0) ? 2 * a.nvec : (a.nvec + c.world - 1) / c.world;
   B200_REQUIRE(need <= a.src_vec, "b200_comm_allreduce: %zu B per source exceed the staging (%zu B)",
                need * 16, src_bytes);
   if (blocks <= 0) {
-    blocks = (int)((need + 1023) / 1024);  // ~16 KB per CTA
-    if (blocks > 128) blocks = 128;
+    const size_t work = (algo == 0) ? a.nvec : (a.nvec + c.world - 1) / c.world;
+    blocks = (int)((work + 2047) / 2048);  // ~32 KB per CTA
+    const int cap = (algo == 0) ? 64 : gmax;
+    if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
   }
   B200_REQUIRE(blocks <= gmax, "b200_comm_allreduce: %d CTAs exceed the flag table (%d)", blocks, gmax);
   B200_REQUIRE(!update || (master && mom && hp), "b200_comm_allreduce: SGD fusion needs state");
   cudaStream_t s = (cudaStream_t)stream;
-#define B200_AR(T, A, U) allreduce_kernel<T, A, U><<<blocks, 256, 0, s>>>(c, a)
+#define B200_AR(T, A, U) allreduce_kernel<T, A, U><<<blocks, AR_THREADS, 0, s>>>(c, a)
   if (dtype == 0) {
     if (algo == 0) { if (update) B200_AR(float, 0, 1); else B200_AR(float, 0, 0); }
     else           { if (update) B200_AR(float, 1, 1); else B200_AR(float, 1, 0); }

@@ -194,3 +194,34 @@ def net_ddp_fused(rank, world, backend, out_dir, use_graph):
                 "losses": eng.last_losses(steps), "steps": eng.steps_done()},
                os.path.join(out_dir, f"net_{rank}.pt"))
     P.destroy_process_group()
+
+
+def mlp_ddp(rank, world, backend, out_dir, algo):
+    """bf16 MLP on tcgen05 GEMMs under DataParallel: per-layer buckets, fused all-reduce +
+    sharded master-weight SGD, overlap with backward."""
+    import importlib
+    P = _pg()
+    DP = importlib.import_module(PKG + ".parallel.data_parallel").DataParallel
+    WideMLP = importlib.import_module(PKG + ".models.mlp").WideMLP
+    comm = P.init_process_group(backend=backend, rank=rank, world_size=world)
+    dev = comm.device
+    torch.manual_seed(50 + rank)
+    model = WideMLP((784, 256, 128, 10)).to(dev)
+    ddp = DP(model, comm, bucket_of=[2, 2, 1, 1, 0, 0], fuse_sgd=(0.1, 0.5, 0.0), algo=algo)
+    init = ddp.flat.param.clone().float().cpu()
+    losses = []
+    for step in range(6):
+        g = torch.Generator().manual_seed(1000 * step + rank)
+        x = torch.randn(32, 784, generator=g).to(torch.bfloat16).to(dev)
+        y = torch.randint(0, 10, (32,), generator=g).to(dev)
+        loss = ddp.loss(x, y)
+        loss.backward()
+        losses.append(loss)
+    torch.cuda.current_stream().wait_stream(ddp.reducer.stream)
+    torch.cuda.synchronize()
+    comm.check_errors()
+    torch.save({"init": init, "final": ddp.flat.param.clone().float().cpu(),
+                "losses": [l.item() for l in losses],
+                "order": ddp.reducer.core.completion_order()},
+               os.path.join(out_dir, f"mlp_{rank}.pt"))
+    P.destroy_process_group()

@@ -45,3 +45,52 @@ def test_net_ddp_fused_peer(native_lib, tmp_path, use_graph):
     launch(_workers.net_ddp_fused, world, args=("b200", str(tmp_path), use_graph), timeout=600)
     res = [torch.load(tmp_path / f"net_{r}.pt") for r in range(world)]
     check_net_ddp(res, world, check_grads=not use_graph)
+
+
+@pytest.mark.parametrize("algo", ["oneshot", "twoshot"])
+def test_mlp_ddp_peer(native_lib, tmp_path, algo):
+    """bf16 MLP: replicas stay bit-identical; result tracks an fp32 single-process oracle."""
+    from csed_514_project_distributed_training_using_pytorch_b200.models.mlp import WideMLP
+    from csed_514_project_distributed_training_using_pytorch_b200.utils.flat import FlatParams
+    world = _world()
+    launch(_workers.mlp_ddp, world, args=("b200", str(tmp_path), algo), timeout=600)
+    res = [torch.load(tmp_path / f"mlp_{r}.pt") for r in range(world)]
+    for r in range(world):
+        assert torch.equal(res[r]["init"], res[0]["init"])
+        assert torch.equal(res[r]["final"], res[0]["final"])
+        assert res[r]["order"] == [0, 1, 2]          # buckets complete back-to-front
+    # fp32 oracle of the same schedule (mean of per-rank gradients, SGD-momentum)
+    torch.manual_seed(50)
+    model = WideMLP((784, 256, 128, 10))
+    flat = FlatParams(model, with_momentum=False)
+    master = flat.param.float().clone()
+    assert torch.equal(master, res[0]["init"])
+    views = flat.views(master)
+    ps = [v.clone().requires_grad_(True) for v in views]
+    bufs = [torch.zeros_like(p) for p in ps]
+    for step in range(6):
+        gs = [torch.zeros_like(p) for p in ps]
+        for r in range(world):
+            g = torch.Generator().manual_seed(1000 * step + r)
+            x = torch.randn(32, 784, generator=g).to(torch.bfloat16).float()
+            y = torch.randint(0, 10, (32,), generator=g)
+            h = x
+            for i in range(3):
+                h = h @ ps[2 * i].to(torch.bfloat16).float().t() + ps[2 * i + 1].to(torch.bfloat16).float()
+                if i < 2:
+                    h = torch.relu(h)
+            for p in ps:
+                p.grad = None
+            torch.nn.functional.cross_entropy(h, y).backward()
+            for a, p in zip(gs, ps):
+                a += p.grad
+        with torch.no_grad():
+            for p, a, b in zip(ps, gs, bufs):
+                b.mul_(0.5).add_(a / world)
+                p.sub_(0.1 * b)
+    for s, p in zip(flat.slots, ps):
+        got = res[0]["final"][s.offset:s.offset + s.numel].view(s.shape)
+        delta_ref = p.detach() - res[0]["init"][s.offset:s.offset + s.numel].view(s.shape)
+        delta_got = got - res[0]["init"][s.offset:s.offset + s.numel].view(s.shape)
+        err = (delta_got - delta_ref).norm() / (delta_ref.norm() + 1e-12)
+        assert err < 0.08, f"update mismatch {err:.3f} for {s.name}"
