@@ -79,8 +79,10 @@ class DataParallel(nn.Module):
 
     def _begin_pass(self):
         if torch.is_grad_enabled() and self.training and self._require_backward_sync:
-            # make sure the previous step's (fused) update is visible to this forward
-            if self.reducer.is_cuda:
+            # make sure the previous step's (fused) update is visible to this forward. Inside
+            # a CUDA-graph capture the previous replay has already joined the side stream
+            # (finalize_backward), and waiting on an un-captured stream is not allowed.
+            if self.reducer.is_cuda and not torch.cuda.is_current_stream_capturing():
                 torch.cuda.current_stream().wait_stream(self.reducer.stream)
             self.reducer.prepare_for_backward()
             self._pass_open = True

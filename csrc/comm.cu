@@ -434,16 +434,23 @@ __device__ __forceinline__ uint4 finish_vec(const AllreduceArgs& a, float* acc, 
   for (int i = 0; i < N; ++i) acc[i] *= a.scale;
   if (UPDATE) {
     const float lr = a.hp[0], mu = a.hp[1], wd = a.hp[2];
-    const size_t e0 = v_global * N - a.state_base;
+    const size_t e0 = v_global * N - a.state_base;   // multiple of N: 16-byte aligned state
+    float4* mw = reinterpret_cast<float4*>(a.master + e0);
+    float4* mb = reinterpret_cast<float4*>(a.mom + e0);
 #pragma unroll
-    for (int i = 0; i < N; ++i) {
-      float w = a.master[e0 + i];
-      const float g = acc[i] + wd * w;
-      const float b = mu * a.mom[e0 + i] + g;
-      a.mom[e0 + i] = b;
-      w -= lr * b;
-      a.master[e0 + i] = w;
-      acc[i] = w;
+    for (int q = 0; q < N / 4; ++q) {
+      float4 w = mw[q], b = mb[q];
+      float* wp = reinterpret_cast<float*>(&w);
+      float* bp = reinterpret_cast<float*>(&b);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float g = acc[4 * q + i] + wd * wp[i];
+        bp[i] = mu * bp[i] + g;
+        wp[i] -= lr * bp[i];
+        acc[4 * q + i] = wp[i];
+      }
+      mw[q] = w;
+      mb[q] = b;
     }
   }
   return Vec<T>::store(acc);

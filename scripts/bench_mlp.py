@@ -79,7 +79,8 @@ try:
 except Exception as e:
     out["ours_graph_error"] = f"{type(e).__name__}: {str(e)[:300]}"
 if comm is not None: comm.check_errors()
-out["ours_loss"] = float(model.loss(x, y)) if comm is None else float(ddp.module.loss(x, y))
+with torch.no_grad():
+    out["ours_loss"] = float(model.loss(x, y))
 
 # ---- torch DDP + NCCL + cuBLAS
 if not a.skip_torch:

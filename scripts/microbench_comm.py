@@ -78,6 +78,42 @@ def main():
                     row[k.replace("_us", "_busGBs")] = 2 * (world - 1) / world * nbytes / (row[k] * 1e-6) / 1e9
             rows.append(row)
         out["sweep"] = rows
+    if what in ("mlp", "all"):
+        from csed_514_project_distributed_training_using_pytorch_b200.models.mlp import WideMLP
+        torch.manual_seed(0)
+        model = WideMLP().to(dev)
+        ddp = DataParallel(model, comm, bucket_of=[2, 2, 1, 1, 0, 0], fuse_sgd=(0.02, 0.5, 0.0), algo="twoshot")
+        B = 512
+        x = torch.randn(B, 784, device=dev).to(torch.bfloat16); y = torch.randint(0, 10, (B,), device=dev)
+        def full():
+            ddp.loss(x, y).backward()
+        def compute_only():
+            with ddp.no_sync():
+                ddp.loss(x, y).backward()
+        def graph_of(fn, join):
+            s = torch.cuda.Stream(); s.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(s):
+                for _ in range(3): fn()
+                if join: torch.cuda.current_stream().wait_stream(ddp.reducer.stream)
+            torch.cuda.current_stream().wait_stream(s); torch.cuda.synchronize(); comm.host_barrier()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=s):
+                fn()
+                if join: torch.cuda.current_stream().wait_stream(ddp.reducer.stream)
+            return g
+        out["mlp_step_graph_us"] = timed(comm, graph_of(full, True).replay, 50)
+        out["mlp_compute_only_graph_us"] = timed(comm, graph_of(compute_only, False).replay, 50)
+        red = ddp.reducer
+        for b in range(red.core.nbuckets):
+            lo, hi = red.ranges[b]
+            def one(b=b):
+                red._launch_bucket(b)
+                torch.cuda.current_stream().wait_stream(red.stream)
+            out[f"bucket{b}_{(hi-lo)*2}B_allreduce_sgd_us"] = timed(comm, one, 50)
+            g = ddp.flat.grad[lo:hi]
+            out[f"bucket{b}_plain_twoshot_us"] = timed(comm, lambda: comm.all_reduce(g, "mean", "twoshot"), 50)
+            xx = torch.randn(hi - lo, device=dev).to(torch.bfloat16)
+            out[f"bucket{b}_nccl_us"] = timed(comm, lambda: dist.all_reduce(xx), 50)
     if rank == 0:
         print(json.dumps(out, indent=1))
     P.destroy_process_group()
