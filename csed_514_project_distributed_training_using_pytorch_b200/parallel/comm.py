@@ -345,9 +345,11 @@ class PeerComm(BaseComm):
         return dict(self._ar, **st)
 
     def choose_algo(self, nbytes: int) -> int:
-        """Measured crossover (profiles/allreduce_sweep.md): one-shot below, two-shot above."""
-        thresh = int(os.environ.get("B200DP_ONESHOT_MAX_KB", "256")) << 10
-        return 0 if nbytes <= thresh else 1
+        """Measured crossover (profiles/allreduce_sweep.md): the tagged one-shot wins while the
+        bytes every rank must absorb, (world-1) x payload, stay small (<= 1 MiB at 2 GPUs,
+        <= 32 KiB at 8); the two-shot wins above."""
+        budget = int(os.environ.get("B200DP_ONESHOT_MAX_KB", "256")) << 10
+        return 0 if nbytes * max(1, self.world_size - 1) <= budget else 1
 
     def all_reduce(self, tensor: torch.Tensor, op: str = "mean", algo="auto", blocks: int = 0,
                    sgd=None):

