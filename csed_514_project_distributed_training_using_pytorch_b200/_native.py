@@ -38,6 +38,7 @@ _SIGS = {
     "b200_conv1_fwd": [c_p, c_p, c_p, c_p, c_p, c_i, c_p],
     "b200_conv1_bwd": [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_p],
     "b200_conv2_fwd": [c_p, c_p, c_p, c_p, c_i, c_f, c_ull, c_ull, c_p, c_p, c_i, c_p],
+    "b200_conv2_fwd_tc": [c_p, c_p, c_p, c_p, c_i, c_f, c_ull, c_ull, c_p, c_p, c_i, c_p],
     "b200_conv2_bwd": [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_p],
     "b200_fc1_fwd": [c_p, c_p, c_p, c_p, c_i, c_f, c_ull, c_ull, c_p, c_i, c_p],
     "b200_fc1_bwd": [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_p],

@@ -28,8 +28,10 @@ class Net(nn.Module):
     PARAM_ORDER = ("conv1.weight", "conv1.bias", "conv2.weight", "conv2.bias",
                    "fc1.weight", "fc1.bias", "fc2.weight", "fc2.bias")
 
-    def __init__(self, dropout_seed: Optional[int] = None):
+    def __init__(self, dropout_seed: Optional[int] = None, conv2_impl: str = "simt"):
         super().__init__()
+        # "simt" (fp32-exact) or "tcgen05" (TF32 implicit GEMM on the tensor cores)
+        self.conv2_impl = conv2_impl
         self.conv1 = nn.Conv2d(1, 10, kernel_size=5)
         self.conv2 = nn.Conv2d(10, 20, kernel_size=5)
         self.conv2_drop = nn.Dropout2d()
@@ -64,7 +66,7 @@ class Net(nn.Module):
         seed, step = self.dropout_seed, self.dropout_step
         a1 = net_ops.conv1_pool_relu(x, self.conv1.weight, self.conv1.bias)
         a2 = net_ops.conv2_drop_pool_relu(a1, self.conv2.weight, self.conv2.bias, m2, mode,
-                                          self.conv2_drop.p, seed, step)
+                                          self.conv2_drop.p, seed, step, self.conv2_impl)
         h1 = net_ops.fc1_relu_drop(a2.view(-1, 320), self.fc1.weight, self.fc1.bias, m3, mode,
                                    0.5, seed, step)
         return net_ops.fc2_log_softmax(h1, self.fc2.weight, self.fc2.bias)

@@ -77,14 +77,16 @@ class Conv1PoolRelu(torch.autograd.Function):
 
 class Conv2DropPoolRelu(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, a1, w, b, mask, mask_mode, p, seed, step):
+    def forward(ctx, a1, w, b, mask, mask_mode, p, seed, step, impl="simt"):
         a1, w, b = _c(a1), _c(w), _c(b)
         B = a1.shape[0]
         a2 = torch.empty(B, 20, 4, 4, dtype=torch.float32, device=a1.device)
         pos2 = torch.empty(B, 20, 4, 4, dtype=torch.uint8, device=a1.device)
         if mask_mode == 1 and mask is None:
             mask = torch.empty(B, 20, dtype=torch.float32, device=a1.device)
-        N.call("b200_conv2_fwd", N.ptr(a1), N.ptr(w), N.ptr(b), N.ptr(mask), mask_mode, float(p),
+        # "tcgen05": TF32 implicit GEMM on the tensor cores (csrc/conv_tcgen05.cu);
+        # "simt": fp32-exact CUDA-core kernel (csrc/net_kernels.cu)
+        N.call("b200_conv2_fwd_tc" if impl == "tcgen05" else "b200_conv2_fwd", N.ptr(a1), N.ptr(w), N.ptr(b), N.ptr(mask), mask_mode, float(p),
                int(seed), int(step), N.ptr(a2), N.ptr(pos2), B, N.stream())
         ctx.save_for_backward(a1, w, a2, pos2, mask if mask_mode else None)
         return a2
@@ -100,7 +102,7 @@ class Conv2DropPoolRelu(torch.autograd.Function):
         N.call("b200_conv2_bwd", N.ptr(a1), N.ptr(w), N.ptr(_c(da2)), N.ptr(a2), N.ptr(pos2),
                N.ptr(mask), N.ptr(dw), N.ptr(db), N.ptr(da1), N.ptr(ws.scratch),
                N.ptr(ws.counter), B, N.stream())
-        return da1, dw, db, None, None, None, None, None
+        return da1, dw, db, None, None, None, None, None, None
 
 
 class Fc1ReluDrop(torch.autograd.Function):
@@ -179,8 +181,8 @@ def conv1_pool_relu(x, w, b):
     return Conv1PoolRelu.apply(x, w, b)
 
 
-def conv2_drop_pool_relu(a1, w, b, mask=None, mask_mode=0, p=0.5, seed=0, step=0):
-    return Conv2DropPoolRelu.apply(a1, w, b, mask, mask_mode, p, seed, step)
+def conv2_drop_pool_relu(a1, w, b, mask=None, mask_mode=0, p=0.5, seed=0, step=0, impl="simt"):
+    return Conv2DropPoolRelu.apply(a1, w, b, mask, mask_mode, p, seed, step, impl)
 
 
 def fc1_relu_drop(a2, W, b, mask=None, mask_mode=0, p=0.5, seed=0, step=0):

@@ -251,3 +251,40 @@ def test_native_runner_matches_python_loop(cuda_device):
     assert torch.equal(out[0][0], out[1][0])
     assert torch.equal(out[0][1], out[1][1])
     assert (out[0][1] > 1.5).all() and (out[0][1] < 3.5).all()
+
+
+@pytest.mark.parametrize("B", [1, 2, 7, 64, 1000])
+def test_conv2_tcgen05_matches_oracle(cuda_device, B):
+    """conv2 + dropout2d + pool + relu on tcgen05 (TF32) vs the fp32 oracle of the layer."""
+    torch.manual_seed(1)
+    net = Net()
+    g = torch.Generator().manual_seed(B)
+    a1 = torch.relu(torch.randn(B, 10, 12, 12, generator=g))
+    m2 = oracle.make_masks(B, g)[0]
+    conv = torch.nn.functional.conv2d(a1.double(), net.conv2.weight.double(), net.conv2.bias.double())
+    want = torch.relu(torch.nn.functional.max_pool2d(conv * m2.double().view(B, 20, 1, 1), 2)).float()
+    got = net_ops.conv2_drop_pool_relu(a1.to(cuda_device), net.conv2.weight.to(cuda_device),
+                                       net.conv2.bias.to(cuda_device), m2.to(cuda_device), 2,
+                                       impl="tcgen05")
+    torch.testing.assert_close(got.cpu(), want, rtol=5e-3, atol=5e-3)   # TF32 inputs
+    # and it agrees with the SIMT kernel to TF32 accuracy, gradients flow through either
+    simt = net_ops.conv2_drop_pool_relu(a1.to(cuda_device), net.conv2.weight.to(cuda_device),
+                                        net.conv2.bias.to(cuda_device), m2.to(cuda_device), 2)
+    torch.testing.assert_close(got, simt, rtol=5e-3, atol=5e-3)
+
+
+def test_net_with_tcgen05_conv2_trains(cuda_device):
+    torch.manual_seed(1)
+    net = Net(conv2_impl="tcgen05").to(cuda_device).train()
+    x, y = _data(64, seed=8)
+    m2, m3 = oracle.make_masks(64, torch.Generator().manual_seed(9))
+    logp = net(x.to(cuda_device), masks=(m2.to(cuda_device), m3.to(cuda_device)))
+    loss = net_ops.nll_loss(logp, y.to(cuda_device))
+    loss.backward()
+    op = _oracle_params(net)
+    lo = oracle.net_loss(op, x.double(), y, m2.double(), m3.double())
+    lo.backward()
+    torch.testing.assert_close(loss.detach().cpu(), lo.detach().float(), rtol=5e-3, atol=5e-3)
+    for p_, q in zip(net.param_list(), op):
+        err = (p_.grad.cpu() - q.grad.float()).norm() / (q.grad.float().norm() + 1e-12)
+        assert err < 2e-2
