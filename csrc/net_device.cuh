@@ -199,13 +199,16 @@ __device__ __forceinline__ void fc2_bwd_img(const float* __restrict__ dlog_s,
                                             const float* __restrict__ m3s,
                                             const float* __restrict__ w4s,
                                             float* __restrict__ dpre_s, float* __restrict__ gW4,
-                                            float* __restrict__ gB4, bool first) {
+                                            float* __restrict__ gB4, bool first,
+                                            bool store = true) {
   const int t = threadIdx.x;
-  for (int o = t; o < W4_SZ; o += NT) {
-    const int c = o / FC1, j = o - c * FC1;
-    gacc(gW4 + o, dlog_s[c] * h1s[j], first);
+  if (store) {
+    for (int o = t; o < W4_SZ; o += NT) {
+      const int c = o / FC1, j = o - c * FC1;
+      gacc(gW4 + o, dlog_s[c] * h1s[j], first);
+    }
+    if (t < NCLS) gacc(gB4 + t, dlog_s[t], first);
   }
-  if (t < NCLS) gacc(gB4 + t, dlog_s[t], first);
   if (t >= 64 && t < 64 + FC1) {
     const int j = t - 64;
     float s = 0.0f;
@@ -224,18 +227,25 @@ __device__ __forceinline__ void fc1_bwd_img(const float* __restrict__ dpre_s,
                                             const float* __restrict__ m2s,
                                             const float* __restrict__ W3,
                                             float* __restrict__ g2s, float* __restrict__ gW3,
-                                            float* __restrict__ gB3, bool first) {
+                                            float* __restrict__ gB3, bool first,
+                                            bool store = true) {
   const int t = threadIdx.x;  // t == k in [0,320)
   const float a = a2s[t];
   float da = 0.0f;
+  if (store) {
 #pragma unroll 10
-  for (int j = 0; j < FC1; ++j) {
-    const float d = dpre_s[j];
-    gacc(gW3 + j * A2_SZ + t, d * a, first);
-    da = fmaf(d, W_SMEM ? W3[j * A2_SZ + t] : __ldg(W3 + j * A2_SZ + t), da);
+    for (int j = 0; j < FC1; ++j) {
+      const float d = dpre_s[j];
+      gacc(gW3 + j * A2_SZ + t, d * a, first);
+      da = fmaf(d, W_SMEM ? W3[j * A2_SZ + t] : __ldg(W3 + j * A2_SZ + t), da);
+    }
+    if (t < FC1) gacc(gB3 + t, dpre_s[t], first);
+  } else {
+#pragma unroll 10
+    for (int j = 0; j < FC1; ++j)
+      da = fmaf(dpre_s[j], W_SMEM ? W3[j * A2_SZ + t] : __ldg(W3 + j * A2_SZ + t), da);
   }
   g2s[t] = (a > 0.0f) ? da * m2s[t >> 4] : 0.0f;
-  if (t < FC1) gacc(gB3 + t, dpre_s[t], first);
 }
 
 // conv2 backward. g2s[20*16] sits at pos2s (arg-max of each pooled window).
@@ -328,118 +338,121 @@ __device__ __forceinline__ void conv1_bwd_img(const float* __restrict__ g1s,
 }
 
 
-// ---- sparse backward (fused step) -------------------------------------------
-// After dropout2d and the ReLUs most of the 320 conv2 window gradients are exactly
-// zero (half the channels are dropped outright), and so are about half of conv1's
-// 1440. The fused step compacts the non-zeros into small lists first and lets the
-// wgrad / dgrad loops run over list lengths instead of fixed 16 / 144 / 3x3x20 trips.
+// ---- backward of the fused step -----------------------------------------------
+// Measured per phase with clock64 (scripts/phase_timing.py): with one image per CTA the
+// backward is LATENCY bound, not instruction bound. Compacted non-zero lists made the loops
+// short but chained dependent shared-memory loads (count -> index -> weight), and cost 3x
+// more cycles than dense, branch-free, vectorised loops. So the fused step uses:
+//   * channel-level sparsity only: a channel dropped by Dropout2d has zero gradient for the
+//     whole image, and the test `m2s[co] == 0` is uniform across the CTA;
+//   * broadcast 16-byte loads of the 16 window gradients / positions of a channel;
+//   * dgrad as a dense [64 pos x 20 ch] x [20 ch x 250] product out of registers (T), then
+//     a 25-tap gather with compile-time offsets.
 
-struct SparseLists {
-  int* nzc_cnt;      // [20]      non-zeros per conv2 output channel
-  uint8_t* nzc_pos;  // [20][16]  their Y*12+X inside a1's 12x12 frame
-  float* nzc_g;      // [20][16]
-  int* lst_cnt;      // [64]      non-zeros per conv2 output position (8x8)
-  uint8_t* lst_co;   // [64][20]  their output channel
-  float* lst_g;      // [64][20]
-  int* cnt1;         // [10]      non-zeros per conv1 channel after in-place compaction
-};
-constexpr int SPARSE_LIST_BYTES = 20 * 4 + 320 + 320 * 4 + 64 * 4 + 1280 + 1280 * 4 + 16 * 4;
-
-__device__ __forceinline__ SparseLists carve_lists(void* base) {
-  SparseLists L;
-  float* f = reinterpret_cast<float*>(base);
-  L.nzc_g = f; f += 320;
-  L.lst_g = f; f += 1280;
-  L.nzc_cnt = reinterpret_cast<int*>(f); f += 20;
-  L.lst_cnt = reinterpret_cast<int*>(f); f += 64;
-  L.cnt1 = reinterpret_cast<int*>(f); f += 16;
-  uint8_t* b = reinterpret_cast<uint8_t*>(f);
-  L.nzc_pos = b; b += 320;
-  L.lst_co = b;
-  return L;
-}
-
-__device__ __forceinline__ void build_conv2_lists(const float* __restrict__ g2s,
+// D[pos][slot] = window gradient of the slot-th LIVE channel if its arg-max sits at conv position
+// pos (8x8 frame), else 0. Every (channel, window) owns exactly one distinct entry: no
+// conflicts. live[] / *nlive_out list the channels Dropout2d kept (all 20 in eval mode).
+__device__ __forceinline__ void build_conv2_dense(const float* __restrict__ g2s,
                                                   const uint8_t* __restrict__ pos2s,
-                                                  const SparseLists& L) {
-  const int t = threadIdx.x, lane = t & 31;
-  {  // per channel: warp w owns channels 2w, 2w+1 (16 lanes each); t == co*16 + p
-    const float g = g2s[t];
-    const unsigned nz = __ballot_sync(0xffffffffu, g != 0.0f);
-    const unsigned half = (lane >> 4) ? (nz >> 16) : (nz & 0xffffu);
-    const int rank = __popc(half & ((1u << (lane & 15)) - 1u));
-    const int co = t >> 4;
-    if (g != 0.0f) {
-      L.nzc_pos[co * 16 + rank] = pos2s[t];
-      L.nzc_g[co * 16 + rank] = g;
-    }
-    if ((lane & 15) == 0) L.nzc_cnt[co] = __popc(half);
+                                                  const float* __restrict__ m2s,
+                                                  float* __restrict__ Ds, int* __restrict__ live,
+                                                  int* __restrict__ slot_of) {
+  const int t = threadIdx.x;  // t == co*16 + p
+  for (int i = t; i < 64 * C2 / 4; i += NT)
+    reinterpret_cast<float4*>(Ds)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (t < 32) {               // warp 0: compact the live channels
+    const bool on = (t < C2) && (m2s[t] != 0.0f);
+    const unsigned bal = __ballot_sync(0xffffffffu, on);
+    const int sl = __popc(bal & ((1u << t) - 1u));
+    if (on) live[sl] = t;
+    if (t < C2) slot_of[t] = on ? sl : -1;
+    if (t == 0) live[C2] = __popc(bal);   // live[20] = count
   }
-  if (t < 64) {  // per conv2 output position: which channels put their window max here
-    const int Y = t >> 3, X = t & 7;
-    const int p = (Y >> 1) * 4 + (X >> 1);
-    const int pos12 = Y * 12 + X;
-    int n = 0;
-#pragma unroll 4
-    for (int co = 0; co < C2; ++co) {
-      const float g = g2s[co * 16 + p];
-      if (pos2s[co * 16 + p] == pos12 && g != 0.0f) {
-        L.lst_co[t * 20 + n] = (uint8_t)co;
-        L.lst_g[t * 20 + n] = g;
-        ++n;
-      }
-    }
-    L.lst_cnt[t] = n;
+  __syncthreads();
+  const int sl = slot_of[t >> 4];
+  if (sl >= 0) {
+    const int pos12 = pos2s[t];
+    const int Y = pos12 / 12, X = pos12 - Y * 12;
+    Ds[(Y * 8 + X) * C2 + sl] = g2s[t];
   }
 }
 
-// conv2 backward over the compacted lists: wgrad, bias grad, and phase 1 of dgrad into
-// T[64][250] (shared memory).
-__device__ __forceinline__ void conv2_bwd_sparse_img(const SparseLists& L,
-                                                     const float* __restrict__ a1s,
-                                                     const float* __restrict__ w2s,
-                                                     float* __restrict__ T,
-                                                     float* __restrict__ gW2,
-                                                     float* __restrict__ gB2, bool first) {
+// conv2 weight / bias gradient: thread <-> one (ci, tap) column, loop over live channels.
+__device__ __forceinline__ void conv2_wgrad_img(const float* __restrict__ g2s,
+                                                const uint8_t* __restrict__ pos2s,
+                                                const float* __restrict__ m2s,
+                                                const float* __restrict__ a1s,
+                                                float* __restrict__ gW2, float* __restrict__ gB2,
+                                                bool first) {
   const int t = threadIdx.x;
   if (t < 250) {
-    // thread <-> one (ci, tap) column r of W2 / T; channel and position loops are
-    // uniform across the CTA, list reads are broadcasts.
-    const int r = t;
-    const int ci = r / 25, kk = r - ci * 25;
+    const int ci = t / 25, kk = t - ci * 25;
     const int ky = kk / 5, kx = kk - ky * 5;
     const float* a = a1s + ci * 144 + ky * 12 + kx;
 #pragma unroll 1
     for (int co = 0; co < C2; ++co) {
-      const int n = L.nzc_cnt[co];
-      if (n == 0 && !first) continue;
-      const float* g = L.nzc_g + co * 16;
-      const uint8_t* ps = L.nzc_pos + co * 16;
       float s = 0.0f;
-      for (int e = 0; e < n; ++e) s = fmaf(g[e], a[ps[e]], s);
-      gacc(gW2 + co * 250 + r, s, first);
-    }
-    // dgrad, phase 1: T[pos][r] = sum over the channels whose window max sits at conv
-    // position `pos` of g * W2[co][ci][tap] (zero for positions nobody selected).
-#pragma unroll 1
-    for (int pos = 0; pos < 64; ++pos) {
-      const int n = L.lst_cnt[pos];
-      const float* g = L.lst_g + pos * 20;
-      const uint8_t* cs = L.lst_co + pos * 20;
-      float s = 0.0f;
-      for (int e = 0; e < n; ++e) s = fmaf(g[e], w2s[(int)cs[e] * 250 + r], s);
-      T[pos * 250 + r] = s;
+      if (m2s[co] != 0.0f) {   // uniform: the whole channel was dropped otherwise
+        const float4* g4 = reinterpret_cast<const float4*>(g2s + co * 16);
+        const uint4 pp = *reinterpret_cast<const uint4*>(pos2s + co * 16);
+        const unsigned pw[4] = {pp.x, pp.y, pp.z, pp.w};
+        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const float4 g = g4[q];
+          s0 = fmaf(g.x, a[pw[q] & 0xffu], s0);
+          s1 = fmaf(g.y, a[(pw[q] >> 8) & 0xffu], s1);
+          s2 = fmaf(g.z, a[(pw[q] >> 16) & 0xffu], s2);
+          s3 = fmaf(g.w, a[pw[q] >> 24], s3);
+        }
+        s = (s0 + s1) + (s2 + s3);
+      } else if (!first) {
+        continue;              // nothing to add to the running partial
+      }
+      gacc(gW2 + co * 250 + t, s, first);
     }
   } else if (t >= 256 && t < 256 + C2) {
     const int co = t - 256;
-    const int n = L.nzc_cnt[co];
     float s = 0.0f;
-    for (int e = 0; e < n; ++e) s += L.nzc_g[co * 16 + e];
+#pragma unroll
+    for (int p = 0; p < 16; ++p) s += g2s[co * 16 + p];
     gacc(gB2 + co, s, first);
   }
 }
 
-// dgrad, phase 2 (after a barrier): g1s[ci][u][v] = sum over the <=25 filter taps of
+// dgrad phase 1: T[pos][r] = sum_co D[pos][co] * W2[co][r], r = ci*25 + tap. D is stored with
+// the LIVE channels (not dropped by Dropout2d) compacted to the front, `live[slot]` names the
+// channel of a slot and nlive is their count; the 4-channel groups beyond nlive are skipped by a
+// uniform branch, so a typical image does 12 instead of 20 FMAs per output.
+__device__ __forceinline__ void conv2_dgrad_T_img(const float* __restrict__ Ds,
+                                                  const int* __restrict__ live, int nlive,
+                                                  const float* __restrict__ w2s,
+                                                  float* __restrict__ T) {
+  const int t = threadIdx.x;
+  if (t >= 250) return;
+  float w[C2];
+#pragma unroll
+  for (int sl = 0; sl < C2; ++sl) w[sl] = (sl < nlive) ? w2s[live[sl] * 250 + t] : 0.0f;
+  const int nq = (nlive + 3) >> 2;
+#pragma unroll 2
+  for (int pos = 0; pos < 64; ++pos) {
+    const float4* d4 = reinterpret_cast<const float4*>(Ds + pos * C2);
+    float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+    for (int q = 0; q < C2 / 4; ++q) {
+      if (q < nq) {   // uniform across the CTA
+        const float4 d = d4[q];
+        s0 = fmaf(d.x, w[4 * q], s0);
+        s1 = fmaf(d.y, w[4 * q + 1], s1);
+        s0 = fmaf(d.z, w[4 * q + 2], s0);
+        s1 = fmaf(d.w, w[4 * q + 3], s1);
+      }
+    }
+    T[pos * 250 + t] = s0 + s1;
+  }
+}
+
+// dgrad phase 2 (after a barrier): g1s[ci][u][v] = sum over the <=25 filter taps of
 // T[(u-ky, v-kx)][ci][tap], with conv1's ReLU mask folded in.
 __device__ __forceinline__ void conv2_dgrad_gather_img(const float* __restrict__ T,
                                                        const float* __restrict__ a1s,
@@ -466,62 +479,41 @@ __device__ __forceinline__ void conv2_dgrad_gather_img(const float* __restrict__
   }
 }
 
-// In-place compaction of conv1's window gradients: warp c squeezes channel c's
-// non-zeros (value + position) to the front of its 144-entry segment.
-__device__ __forceinline__ void compact_conv1_grads(float* __restrict__ g1s,
-                                                    uint16_t* __restrict__ pos1s,
-                                                    const SparseLists& L) {
-  const int c = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  if (c >= C1) return;
-  float* g = g1s + c * 144;
-  uint16_t* ps = pos1s + c * 144;
-  int off = 0;
-  for (int base = 0; base < 144; base += 32) {
-    const int i = base + lane;
-    const float gv = (i < 144) ? g[i] : 0.0f;
-    const uint16_t pv = (i < 144) ? ps[i] : (uint16_t)0;
-    const unsigned nz = __ballot_sync(0xffffffffu, gv != 0.0f);
-    const int rank = __popc(nz & ((1u << lane) - 1u));
-    __syncwarp();
-    if (gv != 0.0f) { g[off + rank] = gv; ps[off + rank] = pv; }
-    off += __popc(nz);
-    __syncwarp();
-  }
-  if (lane == 0) L.cnt1[c] = off;
-}
-
-__device__ __forceinline__ void conv1_bwd_sparse_img(const SparseLists& L,
-                                                     const float* __restrict__ g1s,
-                                                     const uint16_t* __restrict__ pos1s,
-                                                     const float* __restrict__ xs,
-                                                     float* __restrict__ gW1,
-                                                     float* __restrict__ gB1, bool first) {
+// conv1 weight / bias gradient over all 144 windows of a channel, 4 windows per step with
+// 16-byte gradient and 8-byte position broadcasts (zeros contribute nothing).
+__device__ __forceinline__ void conv1_wgrad_img(const float* __restrict__ g1s,
+                                                const uint16_t* __restrict__ pos1s,
+                                                const float* __restrict__ xs,
+                                                float* __restrict__ gW1, float* __restrict__ gB1,
+                                                bool first) {
   const int t = threadIdx.x;
   if (t < W1_SZ) {
     const int c = t / 25, kk = t - c * 25;
     const int ky = kk / 5, kx = kk - ky * 5;
     const float* x = xs + ky * IMG + kx;
-    const float* g = g1s + c * 144;
-    const uint16_t* ps = pos1s + c * 144;
-    const int n = L.cnt1[c];
+    const float4* g4 = reinterpret_cast<const float4*>(g1s + c * 144);
+    const uint2* p2 = reinterpret_cast<const uint2*>(pos1s + c * 144);
     float s0 = 0.0f, s1 = 0.0f, s2 = 0.0f, s3 = 0.0f;
-    int e = 0;
-    for (; e + 3 < n; e += 4) {  // 16-byte value and 8-byte position broadcasts
-      const float4 gv = *reinterpret_cast<const float4*>(g + e);
-      const uint2 pp = *reinterpret_cast<const uint2*>(ps + e);
+#pragma unroll 6
+    for (int e = 0; e < 36; ++e) {
+      const float4 gv = g4[e];
+      const uint2 pp = p2[e];
       s0 = fmaf(gv.x, x[pp.x & 0xffffu], s0);
       s1 = fmaf(gv.y, x[pp.x >> 16], s1);
       s2 = fmaf(gv.z, x[pp.y & 0xffffu], s2);
       s3 = fmaf(gv.w, x[pp.y >> 16], s3);
     }
-    for (; e < n; ++e) s0 = fmaf(g[e], x[ps[e]], s0);
     gacc(gW1 + t, (s0 + s1) + (s2 + s3), first);
   } else if (t >= 256 && t < 256 + C1) {
-    const int c = t - 256;
-    const int n = L.cnt1[c];
-    float s = 0.0f;
-    for (int e = 0; e < n; ++e) s += g1s[c * 144 + e];
-    gacc(gB1 + c, s, first);
+    const float4* g4 = reinterpret_cast<const float4*>(g1s + (t - 256) * 144);
+    float s0 = 0.0f, s1 = 0.0f;
+#pragma unroll 6
+    for (int e = 0; e < 36; ++e) {
+      const float4 g = g4[e];
+      s0 += g.x + g.z;
+      s1 += g.y + g.w;
+    }
+    gacc(gB1 + (t - 256), s0 + s1, first);
   }
 }
 

@@ -27,6 +27,13 @@ using namespace net;
 #define B200_NOALLOC_SCRATCH_BYTES (256 + B200_NOALLOC_MAX_BATCH * B200_NOALLOC_ROW_FLOATS * 4)
 static __device__ __align__(256) unsigned char g_noalloc_scratch[B200_NOALLOC_SCRATCH_BYTES];
 
+// Optional per-phase timestamps of the fused kernel (debug aid; null in production).
+__device__ long long* g_net_phase_dbg = nullptr;
+#define B200_PHASE(i)                                                            \
+  do {                                                                           \
+    if (dbg && threadIdx.x == 0) dbg[blockIdx.x * 16 + (i)] = clock64();         \
+  } while (0)
+
 namespace {
 
 __device__ __forceinline__ float normalize_u8(unsigned v) {
@@ -439,8 +446,8 @@ struct FusedSmem {
 constexpr int FUSED_SMEM_FLOATS = IMG_SZ + A1_SZ + A2_SZ + 64 + 64 + 32 + 16 + 16 + 64 + A2_SZ +
                                   A1_SZ + 252 + 12 + W2_SZ + 20 + W4_SZ + 12 + A1_SZ / 2 +
                                   A2_SZ / 4;
-constexpr int FUSED_LIST_OFF = FUSED_SMEM_FLOATS * 4;
-constexpr int FUSED_T_OFF = FUSED_LIST_OFF + SPARSE_LIST_BYTES;      // T[64][250] floats
+constexpr int FUSED_LIST_OFF = FUSED_SMEM_FLOATS * 4;               // D[64][20] floats
+constexpr int FUSED_T_OFF = FUSED_LIST_OFF + 64 * C2 * 4 + 256;      // + live[21], slot_of[20]; then T[64][250]
 constexpr int FUSED_W3_OFF = FUSED_T_OFF + 64 * 250 * 4;             // fc1.weight staged in smem
 constexpr int FUSED_SMEM_BYTES = FUSED_W3_OFF + W3_SZ * 4;           // ~181 KB: one CTA per SM
 constexpr int EVAL_SMEM_BYTES = FUSED_SMEM_FLOATS * 4;
@@ -493,26 +500,51 @@ net_fwdbwd_kernel(const float* __restrict__ params, const void* __restrict__ x, 
                   float inv_B, float* __restrict__ partial, float* __restrict__ loss_partial,
                   int mask_mode, float* __restrict__ m2buf, float* __restrict__ m3buf,
                   unsigned long long seed, const unsigned long long* __restrict__ step_ptr,
-                  unsigned sample_base, int idx_stride) {
+                  unsigned sample_base, int idx_stride, int split) {
   extern __shared__ __align__(16) float smem[];
   const FusedSmem f = carve(smem);
-  const SparseLists L = carve_lists(smem + FUSED_SMEM_FLOATS);
+  float* Ds = smem + FUSED_SMEM_FLOATS;
+  int* live = reinterpret_cast<int*>(Ds + 64 * C2);   // [21]: live channels, [20] = count
+  int* slot_of = live + 32;                           // [20]
+  // split = 1: two CTAs per image. Both run the (cheap) forward; CTA 2i takes the fc and
+  // conv2 weight gradients, CTA 2i+1 takes conv2's data gradient and conv1's gradients.
+  // They write disjoint parts of the same partial row and never talk to each other, so a
+  // batch of 64 keeps 128 SMs busy instead of 64.
+  const int role = split ? (int)(blockIdx.x & 1) : 2;        // 0: fc+conv2-w, 1: dgrad+conv1, 2: all
+  const int slot = split ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int nslots = split ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+  const bool do_w = role != 1, do_d = role != 0;
+  long long* dbg = g_net_phase_dbg;
+  B200_PHASE(0);
   float* Ts = reinterpret_cast<float*>(reinterpret_cast<char*>(smem) + FUSED_T_OFF);
   float* w3s = reinterpret_cast<float*>(reinterpret_cast<char*>(smem) + FUSED_W3_OFF);
   const int t = threadIdx.x;
-  // fc1.weight (64 KB) streams into shared memory with cp.async while conv1/conv2 run
-  for (int i = t; i < W3_SZ / 4; i += NT) {
-    const unsigned dst = (unsigned)__cvta_generic_to_shared(w3s + i * 4);
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(params + OFF_W3 + i * 4));
-  }
+  // All weights stream into shared memory with cp.async, in the order they are needed, so the
+  // kernel pays ONE global-memory round trip before conv1 instead of a chain of them:
+  //   group 0: conv1 weights/bias      (needed by conv1_fwd)
+  //   group 1: conv2 weights/bias      (needed by conv2_fwd)
+  //   group 2: fc2 weights/bias + fc1.weight (64 KB)   (needed from fc1_fwd on)
+  auto cp16 = [](float* dst, const float* src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(
+                     (unsigned)__cvta_generic_to_shared(dst)),
+                 "l"(src));
+  };
+  if (t < 63) cp16(f.w1s + 4 * t, params + OFF_W1 + 4 * t);
+  if (t >= 64 && t < 67) cp16(f.b1s + 4 * (t - 64), params + OFF_B1 + 4 * (t - 64));
   asm volatile("cp.async.commit_group;" ::: "memory");
-  load_weights(f, params);
+  for (int i = t; i < W2_SZ / 4; i += NT) cp16(f.w2s + 4 * i, params + OFF_W2 + 4 * i);
+  if (t < 5) cp16(f.b2s + 4 * t, params + OFF_B2 + 4 * t);
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  if (t < W4_SZ / 4) cp16(f.w4s + 4 * t, params + OFF_W4 + 4 * t);
+  if (t >= 128 && t < 131) cp16(f.b4s + 4 * (t - 128), params + OFF_B4 + 4 * (t - 128));
+  for (int i = t; i < W3_SZ / 4; i += NT) cp16(w3s + 4 * i, params + OFF_W3 + 4 * i);
+  asm volatile("cp.async.commit_group;" ::: "memory");
   const unsigned long long step = step_ptr ? step_ptr[0] : 0ull;
   if (idx_stride != 0 && step_ptr) gidx += (size_t)(step - step_ptr[1]) * (size_t)idx_stride;
-  float* row = partial + (size_t)blockIdx.x * FLAT_SZ;
+  float* row = partial + (size_t)slot * FLAT_SZ;
   float loss_acc = 0.0f;
   int it = 0;
-  for (int img = blockIdx.x; img < B; img += gridDim.x, ++it) {
+  for (int img = slot; img < B; img += nslots, ++it) {
     const bool first = (it == 0);
     load_image(f.xs, x, x_mode, img, gidx);
     if (t < C2) {
@@ -535,14 +567,20 @@ net_fwdbwd_kernel(const float* __restrict__ params, const void* __restrict__ x, 
       }
       f.m3s[j] = m;
     }
+    if (first) asm volatile("cp.async.wait_group 2;" ::: "memory");
     __syncthreads();
+    B200_PHASE(1);
     conv1_fwd_img(f.xs, f.w1s, f.b1s, f.a1s, f.pos1s);
+    if (first) asm volatile("cp.async.wait_group 1;" ::: "memory");
     __syncthreads();
+    B200_PHASE(2);
     conv2_fwd_img(f.a1s, f.w2s, f.b2s, f.m2s, f.a2s, f.pos2s);
-    if (first) asm volatile("cp.async.wait_all;" ::: "memory");
+    if (first) asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncthreads();
+    B200_PHASE(3);
     fc1_fwd_img<true>(f.a2s, w3s, params + OFF_B3, f.m3s, f.h1s);
     __syncthreads();
+    B200_PHASE(4);
     fc2_fwd_img(f.h1s, f.w4s, f.b4s, f.logit_s);
     __syncthreads();
     if (t == 0) {
@@ -560,27 +598,50 @@ net_fwdbwd_kernel(const float* __restrict__ params, const void* __restrict__ x, 
       loss_acc -= lt * inv_B;
     }
     __syncthreads();
-    fc2_bwd_img(f.dlog_s, f.h1s, f.m3s, f.w4s, f.dpre_s, row + OFF_W4, row + OFF_B4, first);
+    B200_PHASE(5);
+    fc2_bwd_img(f.dlog_s, f.h1s, f.m3s, f.w4s, f.dpre_s, row + OFF_W4, row + OFF_B4, first, do_w);
     __syncthreads();
-    fc1_bwd_img<true>(f.dpre_s, f.a2s, f.m2s, w3s, f.g2s, row + OFF_W3, row + OFF_B3, first);
+    B200_PHASE(6);
+    fc1_bwd_img<true>(f.dpre_s, f.a2s, f.m2s, w3s, f.g2s, row + OFF_W3, row + OFF_B3, first, do_w);
     __syncthreads();
-    build_conv2_lists(f.g2s, f.pos2s, L);
+    B200_PHASE(7);
+    if (do_d) build_conv2_dense(f.g2s, f.pos2s, f.m2s, Ds, live, slot_of);   // uniform per CTA
     __syncthreads();
-    conv2_bwd_sparse_img(L, f.a1s, f.w2s, Ts, row + OFF_W2, row + OFF_B2, first);
+    B200_PHASE(8);
+    if (do_w) conv2_wgrad_img(f.g2s, f.pos2s, f.m2s, f.a1s, row + OFF_W2, row + OFF_B2, first);
+    if (do_d) conv2_dgrad_T_img(Ds, live, live[C2], f.w2s, Ts);
     __syncthreads();
-    conv2_dgrad_gather_img(Ts, f.a1s, f.g1s);
-    __syncthreads();
-    compact_conv1_grads(f.g1s, f.pos1s, L);
-    __syncthreads();
-    conv1_bwd_sparse_img(L, f.g1s, f.pos1s, f.xs, row + OFF_W1, row + OFF_B1, first);
-    __syncthreads();
+    B200_PHASE(9);
+    if (do_d) {
+      conv2_dgrad_gather_img(Ts, f.a1s, f.g1s);
+      __syncthreads();
+      B200_PHASE(10);
+      conv1_wgrad_img(f.g1s, f.pos1s, f.xs, row + OFF_W1, row + OFF_B1, first);
+      __syncthreads();
+      B200_PHASE(12);
+    }
   }
-  if (t == 0) loss_partial[blockIdx.x] = loss_acc;
-  // zero the 8 pad floats of the row so the flat reduction never reads garbage
-  if (t < 2) row[OFF_W1 + W1_SZ + t] = 0.0f;
-  if (t >= 2 && t < 4) row[OFF_B1 + B1_SZ + (t - 2)] = 0.0f;
-  if (t >= 4 && t < 6) row[OFF_B3 + B3_SZ + (t - 4)] = 0.0f;
-  if (t >= 6 && t < 8) row[OFF_B4 + B4_SZ + (t - 6)] = 0.0f;
+  // Next step's batch is known already (device-side index stepping): pull its rows from HBM
+  // into L2 now, off the critical path of the next launch.
+  if (idx_stride != 0 && x_mode >= 2 && role != 1) {
+    const int* nidx = gidx + idx_stride;
+    const size_t row_bytes = (x_mode == 3) ? IMG_SZ * 4 : IMG_SZ;
+    const int lines = (int)((row_bytes + 127) / 128);
+    for (int img = slot; img < B; img += nslots)
+      if (t < lines) {
+        const char* p = (const char*)x + (size_t)nidx[img] * row_bytes + (size_t)t * 128;
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+      }
+  }
+  B200_PHASE(13);
+  if (role != 1) {
+    if (t == 0) loss_partial[slot] = loss_acc;
+    // zero the 8 pad floats of the row so the flat reduction never reads garbage
+    if (t < 2) row[OFF_W1 + W1_SZ + t] = 0.0f;
+    if (t >= 2 && t < 4) row[OFF_B1 + B1_SZ + (t - 2)] = 0.0f;
+    if (t >= 4 && t < 6) row[OFF_B3 + B3_SZ + (t - 4)] = 0.0f;
+    if (t >= 6 && t < 8) row[OFF_B4 + B4_SZ + (t - 6)] = 0.0f;
+  }
 }
 
 // Fused whole-step kernel B (single GPU): fixed-order sum of the partial rows, then
@@ -823,6 +884,13 @@ int b200_sgd_momentum(float* p, const float* g, float* buf, long long n, const f
   return 0;
 }
 
+// Debug: per-CTA, per-phase clock64() stamps of the next fused kernel launches go to `buf`
+// (device, >= grid*16 int64); pass null to switch off.
+int b200_net_set_phase_debug(long long* buf) {
+  B200_CUDA_OK(cudaMemcpyToSymbol(g_net_phase_dbg, &buf, sizeof(buf)));
+  return 0;
+}
+
 // Rows (CTAs) the fused step uses for a batch of B images.
 int b200_net_fused_rows(int B) { return grid_for(B, 148); }
 
@@ -851,9 +919,12 @@ int b200_net_fwdbwd(const float* params, const void* x, int x_mode, const long l
   B200_REQUIRE(mask_mode != 2 || (m2buf && m3buf), "b200_net_fwdbwd: mask_mode 2 needs both masks");
   B200_REQUIRE(x_mode < 2 || gidx != nullptr, "b200_net_fwdbwd: gather modes need an index buffer");
   if (int e = ensure_fused_attr()) return e;
-  net_fwdbwd_kernel<<<grid_for(B, 148), NT, FUSED_SMEM_BYTES, (cudaStream_t)stream>>>(
+  // when the batch leaves at least half of the 148 SMs idle, give every image two CTAs
+  const int split = (2 * B <= 148) ? 1 : 0;
+  const int grid = split ? 2 * B : grid_for(B, 148);
+  net_fwdbwd_kernel<<<grid, NT, FUSED_SMEM_BYTES, (cudaStream_t)stream>>>(
       params, x, x_mode, labels, gidx, B, 1.0f / (float)B, partial, loss_partial, mask_mode, m2buf,
-      m3buf, seed, step_ptr, sample_base, idx_stride);
+      m3buf, seed, step_ptr, sample_base, idx_stride, split);
   B200_LAUNCH_OK();
   return 0;
 }
