@@ -125,20 +125,26 @@ def run_ours(a):
     perm = torch.randperm(N_TRAIN, generator=torch.Generator().manual_seed(42))[rank::world][:shard]
     perm = perm.to(torch.int32).to(dev)
     steps_per_epoch = shard // B
+    U = 16   # steps per captured graph (programmatic dependent launch spans step boundaries)
     if a.no_graph:
         def one():
             eng.step(dx, dy, X_F32_GATHER, gidx=perm, batch=B, idx_stride=B)
+        multi = None
     else:
-        graph = eng.capture(dx, dy, X_F32_GATHER, gidx=perm, batch=B, idx_stride=B)
-        one = graph.replay
+        one = eng.capture(dx, dy, X_F32_GATHER, gidx=perm, batch=B, idx_stride=B).replay
+        multi = eng.capture(dx, dy, X_F32_GATHER, gidx=perm, batch=B, idx_stride=B, unroll=U).replay
 
     def run_steps(n):
         done = 0
         while done < n:
             eng.begin_epoch()
             m = min(steps_per_epoch, n - done)
-            for _ in range(m):
-                one()
+            i = 0
+            while i < m:
+                if multi is not None and m - i >= U:
+                    multi(); i += U
+                else:
+                    one(); i += 1
             done += m
 
     def sync_all():
@@ -196,7 +202,8 @@ def run_ours(a):
     clocks = sampler.stop() if sampler is not None else None
     if rank == 0:
         result_line(a, "ours", value, ms / K, e2e, clocks, launches,
-                    {"cuda_graph": not a.no_graph, "kernels_per_step": kernels_per_step,
+                    {"cuda_graph": not a.no_graph, "steps_per_graph": 1 if a.no_graph else U,
+                     "kernels_per_step": kernels_per_step,
                      "last_losses": eng.last_losses(2).tolist()})
     if comm is not None:
         P.destroy_process_group()

@@ -133,12 +133,17 @@ class FusedNetEngine:
         self.reduce_and_update(B, write_grad=write_grad)
 
     # -- CUDA graph ----------------------------------------------------------
-    def capture(self, x, y, x_mode=X_F32, gidx=None, batch=None, key=None, idx_stride=0):
+    def capture(self, x, y, x_mode=X_F32, gidx=None, batch=None, key=None, idx_stride=0,
+                unroll: int = 1):
         """Capture one step reading the given static input tensors; returns the graph.
 
         Replay with `graph.replay()` after copying new data into x / y (/ gidx).
         Kernel arguments are baked in; step counter, learning rate and the loss ring
         index live in device memory, so replays advance them correctly.
+
+        unroll > 1 captures that many consecutive steps in one graph. It only makes sense
+        with device-side index stepping (idx_stride != 0), where every step finds its own
+        batch; the programmatic-dependent-launch edges then span step boundaries too.
         """
         s = torch.cuda.Stream(device=self.device)
         s.wait_stream(torch.cuda.current_stream())
@@ -152,8 +157,10 @@ class FusedNetEngine:
         g = torch.cuda.CUDAGraph()
         launches_before = self.launches
         with torch.cuda.graph(g, stream=s):
-            self.step(x, y, x_mode, gidx, batch=batch, idx_stride=idx_stride)
+            for _ in range(max(1, unroll)):
+                self.step(x, y, x_mode, gidx, batch=batch, idx_stride=idx_stride)
         g.kernels_per_replay = self.launches - launches_before
+        g.steps_per_replay = max(1, unroll)
         self.launches = launches_before
         if key is not None:
             self._graphs[key] = g

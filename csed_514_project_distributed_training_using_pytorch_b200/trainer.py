@@ -153,12 +153,14 @@ class Trainer:
             return self._train_epoch_fused(epoch, sampler)
         return self._train_epoch_autograd(epoch, sampler)
 
-    def _graph_for(self, B: int, data: MNISTArrays):
-        g = self._graphs.get(B)
+    UNROLL = 16   # steps per captured graph in the resident path (PDL spans step boundaries)
+
+    def _graph_for(self, B: int, data: MNISTArrays, unroll: int = 1):
+        g = self._graphs.get((B, unroll))
         if g is None:
             g = self.engine.capture(data.images, data.labels, X_U8_GATHER, gidx=self._perm_dev,
-                                    batch=B, idx_stride=self._stride)
-            self._graphs[B] = g
+                                    batch=B, idx_stride=self._stride, unroll=unroll)
+            self._graphs[(B, unroll)] = g
         return g
 
     def _train_epoch_fused(self, epoch: int, sampler: ShardSampler) -> float:
@@ -179,6 +181,7 @@ class Trainer:
         eng.begin_epoch()
         use_graph = c.cuda_graph
         g_full = self._graph_for(B, data) if (use_graph and full > 0) else None
+        g_multi = self._graph_for(B, data, self.UNROLL) if (use_graph and full >= self.UNROLL) else None
         epoch_loss = 0.0
         li = c.log_interval
         n_dataset = len(self.train_set)
@@ -204,16 +207,23 @@ class Trainer:
                                        bi * 64 + (epoch - 1) * n_dataset)
             pending = 0
 
-        chunk = min(eng.ring, max(li, 256))
-        for bi in range(full):
-            if g_full is not None:
+        chunk = min(eng.ring - self.UNROLL, max(li, 256))
+        bi = 0
+        while bi < full:
+            if g_multi is not None and full - bi >= self.UNROLL:
+                g_multi.replay()
+                n = self.UNROLL
+            elif g_full is not None:
                 g_full.replay()
+                n = 1
             else:
                 eng.step(data.images, data.labels, X_U8_GATHER, gidx=self._perm_dev, batch=B,
                          idx_stride=B)
-            pending += 1
+                n = 1
+            bi += n
+            pending += n
             if pending >= chunk:
-                flush(bi + 1)
+                flush(bi)
                 if not self.distributed_style and c.checkpoint_every_log:
                     self.save()
         if tail:

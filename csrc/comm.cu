@@ -25,6 +25,8 @@ using namespace net;
 // ===========================================================================
 // Host: symmetric memory
 // ===========================================================================
+extern "C" int b200_pdl_enabled(void);
+
 extern "C" {
 
 int b200_symm_alloc(size_t bytes, void** dptr, unsigned char* handle64) {
@@ -220,6 +222,8 @@ net_reduce_allreduce_sgd_kernel(CommDev c, const float* __restrict__ partial, in
   const int cidx = threadIdx.x & 31, rg = threadIdx.x >> 5;
   const int col = blockIdx.x * 32 + cidx;
   const bool valid = col < N4;
+  pdl_trigger();
+  pdl_wait();
   const unsigned seq = *seq_ctr + 1u;  // every CTA reads it before the last one bumps it
   const unsigned slot = seq & 1u;
   const float4 s = sum_partial_rows_256(partial, G, FLAT_SZ, col, valid, sm);
@@ -297,6 +301,8 @@ net_reduce_allreduce_sgd_ll_kernel(CommDev c, const float* __restrict__ partial,
   const int cidx = threadIdx.x & 31, rg = threadIdx.x >> 5;
   const int col = blockIdx.x * 32 + cidx;
   const bool valid = col < N4;
+  pdl_trigger();   // the next step's kernel A may start launching
+  pdl_wait();      // partial rows come from kernel A; seq_ctr from the previous kernel B
   const unsigned seq = *seq_ctr + 1u;
   const unsigned slot = seq & 1u;
   const float4 s = sum_partial_rows_256(partial, G, FLAT_SZ, col, valid, sm);
@@ -715,15 +721,17 @@ int b200_comm_net_reduce_allreduce_sgd(const void* comm, const float* partial, i
   const CommDev& c = *(const CommDev*)comm;
   B200_REQUIRE(rows > 0 && rows <= 148, "b200_comm_net_reduce_allreduce_sgd: rows out of range");
   const int blocks = (FLAT_SZ / 4 + 31) / 32;
+  const bool pdl = b200_pdl_enabled() != 0;
   if (protocol == 0)   // low latency: tagged payload words
-    net_reduce_allreduce_sgd_ll_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(
-        c, partial, rows, params, mom, grad_out, hp, loss_partial, loss_ring, ring, ctl, stage_off,
-        seq_ctr, arrive_ctr);
+    B200_CUDA_OK(b200_launch_pdl(net_reduce_allreduce_sgd_ll_kernel, dim3(blocks), dim3(256), 0,
+                                 (cudaStream_t)stream, pdl, c, partial, rows, params, mom, grad_out,
+                                 hp, loss_partial, loss_ring, ring, ctl, stage_off, seq_ctr,
+                                 arrive_ctr));
   else                 // payload, system fence, then a flag per CTA
-    net_reduce_allreduce_sgd_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(
-        c, partial, rows, params, mom, grad_out, hp, loss_partial, loss_ring, ring, ctl, stage_off,
-        flag_off, seq_ctr, arrive_ctr);
-  B200_LAUNCH_OK();
+    B200_CUDA_OK(b200_launch_pdl(net_reduce_allreduce_sgd_kernel, dim3(blocks), dim3(256), 0,
+                                 (cudaStream_t)stream, pdl, c, partial, rows, params, mom, grad_out,
+                                 hp, loss_partial, loss_ring, ring, ctl, stage_off, flag_off,
+                                 seq_ctr, arrive_ctr));
   return 0;
 }
 

@@ -6,6 +6,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 // ---------------------------------------------------------------------------
 // Error reporting for the C ABI. Every exported function returns 0 on success
@@ -42,6 +43,36 @@ extern "C" void b200_set_error(const char* fmt, ...);
   } while (0)
 
 #ifdef __CUDACC__
+
+// ---------------------------------------------------------------------------
+// Programmatic dependent launch (PDL). A kernel launched with b200_launch_pdl may start
+// (its CTAs become resident) while its predecessor in the stream is still running; it must
+// call pdl_wait() before touching anything the predecessor writes. pdl_trigger() lets the
+// NEXT kernel start launching. Used by the two kernels of the fused step so the ~2 us
+// launch latency at each kernel boundary overlaps the previous kernel's execution.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ void pdl_trigger() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+__device__ __forceinline__ void pdl_wait() {
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t b200_launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                                   cudaStream_t stream, bool pdl, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
 
 // ---------------------------------------------------------------------------
 // Warp helpers

@@ -16,6 +16,8 @@
 
 using namespace net;
 
+extern "C" int b200_pdl_enabled(void);
+
 // ---------------------------------------------------------------------------
 // Built-in scratch for b200_conv1_bwd_noalloc (see the entry point at the end of this
 // file). It lives in the library image: every GPU that loads the library carries these
@@ -515,6 +517,8 @@ net_fwdbwd_kernel(const float* __restrict__ params, const void* __restrict__ x, 
   const int nslots = split ? (int)(gridDim.x >> 1) : (int)gridDim.x;
   const bool do_w = role != 1, do_d = role != 0;
   long long* dbg = g_net_phase_dbg;
+  pdl_trigger();   // kernel B of this step may start launching now
+  pdl_wait();      // ... and this kernel may not read parameters before the previous B is done
   B200_PHASE(0);
   float* Ts = reinterpret_cast<float*>(reinterpret_cast<char*>(smem) + FUSED_T_OFF);
   float* w3s = reinterpret_cast<float*>(reinterpret_cast<char*>(smem) + FUSED_W3_OFF);
@@ -655,6 +659,8 @@ net_reduce_sgd_kernel(const float* __restrict__ partial, int G, float* __restric
   __shared__ float4 sm[8][32];
   constexpr int N4 = FLAT_SZ / 4;
   const int i = blockIdx.x * 32 + (threadIdx.x & 31);
+  pdl_trigger();   // the next step's kernel A may start launching
+  pdl_wait();      // partial rows come from kernel A
   const float4 s = sum_partial_rows_256(partial, G, FLAT_SZ, i, i < N4, sm);
   if (threadIdx.x < 32 && i < N4) {
     if (grad_out) reinterpret_cast<float4*>(grad_out)[i] = s;
@@ -891,6 +897,16 @@ int b200_net_set_phase_debug(long long* buf) {
   return 0;
 }
 
+// PDL on the fused step's kernels (B200DP_PDL=0 switches it off).
+int b200_pdl_enabled(void) {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("B200DP_PDL");
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v;
+}
+
 // Rows (CTAs) the fused step uses for a batch of B images.
 int b200_net_fused_rows(int B) { return grid_for(B, 148); }
 
@@ -922,10 +938,10 @@ int b200_net_fwdbwd(const float* params, const void* x, int x_mode, const long l
   // when the batch leaves at least half of the 148 SMs idle, give every image two CTAs
   const int split = (2 * B <= 148) ? 1 : 0;
   const int grid = split ? 2 * B : grid_for(B, 148);
-  net_fwdbwd_kernel<<<grid, NT, FUSED_SMEM_BYTES, (cudaStream_t)stream>>>(
-      params, x, x_mode, labels, gidx, B, 1.0f / (float)B, partial, loss_partial, mask_mode, m2buf,
-      m3buf, seed, step_ptr, sample_base, idx_stride, split);
-  B200_LAUNCH_OK();
+  B200_CUDA_OK(b200_launch_pdl(net_fwdbwd_kernel, dim3(grid), dim3(NT), FUSED_SMEM_BYTES,
+                               (cudaStream_t)stream, b200_pdl_enabled(), params, x, x_mode, labels,
+                               gidx, B, 1.0f / (float)B, partial, loss_partial, mask_mode, m2buf,
+                               m3buf, seed, step_ptr, sample_base, idx_stride, split));
   return 0;
 }
 
@@ -935,9 +951,9 @@ int b200_net_reduce_sgd(const float* partial, int rows, float* params, float* mo
                         unsigned long long* step_ptr, void* stream) {
   B200_REQUIRE(rows > 0 && rows <= 148, "b200_net_reduce_sgd: rows out of range");
   const int blocks = (FLAT_SZ / 4 + 31) / 32;
-  net_reduce_sgd_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(
-      partial, rows, params, mom, grad_out, hp, loss_partial, loss_ring, ring, step_ptr);
-  B200_LAUNCH_OK();
+  B200_CUDA_OK(b200_launch_pdl(net_reduce_sgd_kernel, dim3(blocks), dim3(256), 0,
+                               (cudaStream_t)stream, b200_pdl_enabled(), partial, rows, params, mom,
+                               grad_out, hp, loss_partial, loss_ring, ring, step_ptr));
   return 0;
 }
 

@@ -55,6 +55,16 @@ def main():
         torch.cuda.synchronize()
         out[f"epoch_resident_ms_rep{rep}"] = a.elapsed_time(b)
     out["epoch_last_losses"] = eng.last_losses(3).tolist()
+    for U in (4, 16):
+        gU = eng.capture(data, labels, X_F32_GATHER, gidx=perm, batch=64, idx_stride=64, unroll=U)
+        for rep in range(2):
+            eng.begin_epoch()
+            a.record()
+            for _ in range(steps // U):
+                gU.replay()
+            b.record()
+            torch.cuda.synchronize()
+        out[f"epoch_resident_unroll{U}_ms"] = a.elapsed_time(b) * steps / (steps // U * U)
     # eval 10k
     xe = torch.randn(1000, 1, 28, 28, device=dev)
     ye = torch.randint(0, 10, (1000,), device=dev)
