@@ -225,3 +225,27 @@ def mlp_ddp(rank, world, backend, out_dir, algo):
                 "order": ddp.reducer.core.completion_order()},
                os.path.join(out_dir, f"mlp_{rank}.pt"))
     P.destroy_process_group()
+
+
+def trainer_dist(rank, world, backend, out_dir):
+    """The reference's train_dist.py script body on `world` ranks (src/train_dist.py:118-164)."""
+    import importlib
+    P = _pg()
+    Trainer = importlib.import_module(PKG + ".trainer").Trainer
+    TrainConfig = importlib.import_module(PKG + ".utils.config").TrainConfig
+    MetricsLogger = importlib.import_module(PKG + ".utils.metrics").MetricsLogger
+    synthetic = importlib.import_module(PKG + ".utils.data").synthetic_mnist
+    comm = P.init_process_group(backend=backend, rank=rank, world_size=world)
+    cfg = TrainConfig(epochs=2, learning_rate=0.05, world_size=world, rank=rank, train_size=2048 + 24,
+                      test_size=500, batch_size_test=250, results_dir=os.path.join(out_dir, "results"),
+                      images_dir=os.path.join(out_dir, f"images{rank}"),
+                      device="cpu" if backend == "gloo" else "cuda")
+    tr = Trainer(cfg, comm=comm, logger=MetricsLogger(rank=rank, quiet=True), distributed_style=True)
+    tr.set_data(synthetic(cfg.train_size, seed=0), synthetic(cfg.test_size, seed=1))
+    log = tr.fit()
+    if comm.device.type == "cuda":
+        torch.cuda.synchronize()
+        comm.check_errors()
+    torch.save({"param": tr.flat.param.clone().cpu(), "test_losses": log.test_losses,
+                "n_train_losses": len(log.train_losses)}, os.path.join(out_dir, f"tr_{rank}.pt"))
+    P.destroy_process_group()

@@ -50,3 +50,12 @@ def test_ddp_generic_gloo(tmp_path):
         launch(_workers.ddp_generic, 2, args=("gloo", str(d), fuse, "auto"), timeout=180)
         res = [torch.load(d / f"ddp_{r}.pt") for r in range(2)]
         check_ddp_generic(res, 2)
+
+
+def test_trainer_distributed_gloo(tmp_path):
+    launch(_workers.trainer_dist, 2, args=("gloo", str(tmp_path)), timeout=300)
+    res = [torch.load(tmp_path / f"tr_{r}.pt") for r in range(2)]
+    assert torch.equal(res[0]["param"], res[1]["param"])
+    assert res[0]["test_losses"][-1] < res[0]["test_losses"][0]
+    assert res[0]["n_train_losses"] == 2 * 33
+    assert (tmp_path / "results" / "model.pt").exists()

@@ -94,3 +94,16 @@ def test_mlp_ddp_peer(native_lib, tmp_path, algo):
         delta_got = got - res[0]["init"][s.offset:s.offset + s.numel].view(s.shape)
         err = (delta_got - delta_ref).norm() / (delta_ref.norm() + 1e-12)
         assert err < 0.3, f"update mismatch {err:.3f} for {s.name}"
+
+
+def test_trainer_distributed_peer(native_lib, tmp_path):
+    world = 2 if torch.cuda.device_count() >= 2 else 0
+    if not world:
+        pytest.skip("needs 2 GPUs")
+    launch(_workers.trainer_dist, world, args=("b200", str(tmp_path)), timeout=600)
+    res = [torch.load(tmp_path / f"tr_{r}.pt") for r in range(world)]
+    assert torch.equal(res[0]["param"], res[1]["param"])            # replicas never diverge
+    assert res[0]["test_losses"][-1] < res[0]["test_losses"][0]     # and the model learns
+    # per-rank batch int(64/2) = 32 over a shard of 1036 samples: 33 batches per epoch
+    assert res[0]["n_train_losses"] == 2 * 33
+    assert (tmp_path / "results" / "model.pt").exists()             # rank 0 only
