@@ -56,7 +56,12 @@ class LinearFn(torch.autograd.Function):
             # dgrad reads W, so it must be queued before the bucket kernel may update W
             dx = gemm.linear_dgrad(dyv, W, relu_mask=x if mask_in else None)
         if sink is not None:
-            gemm.gemm_bf16(dyv, x, True, True, out=sink.view(iw))
+            rs = sink.rs_target(iw) if hasattr(sink, "rs_target") else None
+            # fused GEMM -> reduce-scatter: the wgrad epilogue stores each result vector into
+            # the staging slot of the rank that owns it, over NVLink, tile by tile
+            gemm.gemm_bf16(dyv, x, True, True, out=sink.view(iw), rs=rs)
+            if rs is not None:
+                sink.mark_pushed(rs)
             N.call("b200_colsum_bf16", N.ptr(dyv), dyv.stride(0), N.ptr(sink.view(ib)),
                    dyv.shape[0], n_out, N.stream())
             sink.ready(iw)

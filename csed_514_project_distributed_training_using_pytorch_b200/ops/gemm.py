@@ -12,9 +12,12 @@ import torch
 from .. import _native as N
 
 c_p, c_i, c_ll = C.c_void_p, C.c_int, C.c_longlong
+c_sz = C.c_size_t
 N.register_sigs({
     "b200_gemm_bf16": [c_p, c_i, c_ll, c_p, c_i, c_ll, c_p, c_i, c_ll, c_i, c_i, c_i, c_p, c_i,
                        c_p, c_ll, c_p],
+    "b200_gemm_bf16_rs": [c_p, c_i, c_ll, c_p, c_i, c_ll, c_p, c_i, c_ll, c_i, c_i, c_i, c_p, c_i,
+                          c_p, c_ll, c_p, c_sz, c_sz, c_sz, c_sz, c_p, c_p],
 })
 
 
@@ -29,10 +32,13 @@ def _chk(t: torch.Tensor, name: str):
 def gemm_bf16(A: torch.Tensor, B: torch.Tensor, a_mn: bool = False, b_mn: bool = False,
               out: Optional[torch.Tensor] = None, out_dtype=torch.bfloat16,
               bias: Optional[torch.Tensor] = None, relu: bool = False,
-              relu_mask: Optional[torch.Tensor] = None, n_valid: Optional[int] = None):
+              relu_mask: Optional[torch.Tensor] = None, n_valid: Optional[int] = None,
+              rs: Optional[dict] = None):
     """C[M,N] = op(A) op(B)^T, fp32 accumulate.
     a_mn=False: A is [M,K]; True: A is [K,M].  b_mn=False: B is [N,K]; True: B is [K,N].
-    n_valid limits N (and M for a_mn) to a prefix of a padded operand."""
+    n_valid limits N (and M for a_mn) to a prefix of a padded operand.
+    rs (from PeerComm.rs_target + 'base_vec'): fused reduce-scatter epilogue, the result is
+    scattered to the owner ranks' staging instead of being written to `out`."""
     _chk(A, "A"); _chk(B, "B")
     if a_mn:
         K, M = A.shape
@@ -57,6 +63,12 @@ def gemm_bf16(A: torch.Tensor, B: torch.Tensor, a_mn: bool = False, b_mn: bool =
         raise N.NativeError("gemm: bias must be bf16 with at least N elements")
     if relu_mask is not None and (relu_mask.dtype != torch.bfloat16 or relu_mask.stride(1) != 1):
         raise N.NativeError("gemm: relu_mask must be a bf16 matrix")
+    if rs is not None:
+        N.call("b200_gemm_bf16_rs", N.ptr(A), int(a_mn), A.stride(0), N.ptr(B), int(b_mn),
+               B.stride(0), N.ptr(out), c_fp32, out.stride(0), M, Nn, K, None, 0, None, 0,
+               rs["comm"], rs["stage_off"], rs["src_bytes"], rs["slice_vec"], rs["base_vec"],
+               rs["seq"], N.stream())
+        return out
     N.call("b200_gemm_bf16", N.ptr(A), int(a_mn), A.stride(0), N.ptr(B), int(b_mn), B.stride(0),
            N.ptr(out), c_fp32, out.stride(0), M, Nn, K, N.ptr(bias), int(relu), N.ptr(relu_mask),
            relu_mask.stride(0) if relu_mask is not None else 0, N.stream())

@@ -47,7 +47,7 @@ N.register_sigs({
     "b200_comm_net_reduce_allreduce_sgd": [c_p, c_p, c_i, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_p,
                                            c_sz, c_sz, c_p, c_p, c_i, c_p],
     "b200_comm_allreduce": [c_p, c_i, c_i, c_i, c_p, c_p, c_sz, c_sz, c_sz, c_sz, c_sz, c_i, c_p,
-                            c_p, c_f, c_p, c_p, c_p, c_sz, c_i, c_p],
+                            c_p, c_f, c_p, c_p, c_p, c_sz, c_i, c_sz, c_p],
 }, {"b200_comm_net_stage_bytes": c_sz, "b200_comm_net_flag_bytes": c_sz})
 
 MAX_WORLD = 8
@@ -323,26 +323,42 @@ class PeerComm(BaseComm):
     # -- generic all-reduce ----------------------------------------------------
     GMAX = 256
 
-    def _ar_channel(self, algo: int, src_bytes_needed: int):
-        """Staging + flags of the generic all-reduce. The tagged-word (one-shot) and the bulk
-        (two-shot) protocols get SEPARATE staging: a stale bulk payload word must never be
-        mistaken for a sequence tag."""
+    def _ar_channel(self, algo: int, src_bytes_needed: int, channel: int = 0):
+        """Flags, counters and staging of all-reduce channel `channel`. Collectives on one
+        channel are serialised by their sequence counter; independent streams of collectives
+        (e.g. one per gradient bucket) use different channels. The tagged-word (one-shot) and
+        bulk (two-shot) protocols get SEPARATE staging: a stale bulk payload word must never
+        be mistaken for a sequence tag."""
         if self._ar is None:
-            self._ar = {"flags": self._region(2 * self.GMAX * MAX_WORLD * 4),
-                        "seq": self._counter(), "arrive": self._counter(), "stages": {}}
+            self._ar = {}
+        ch = self._ar.get(channel)
+        if ch is None:
+            ch = self._ar[channel] = {"flags": self._region(2 * self.GMAX * MAX_WORLD * 4),
+                                      "seq": self._counter(), "arrive": self._counter(),
+                                      "stages": {}}
             torch.cuda.synchronize(self.device)
             self.host_barrier()
-        st = self._ar["stages"].get(algo)
+        st = ch["stages"].get(algo)
         if st is None or st["src_bytes"] < src_bytes_needed:
-            floor_mb = "1" if algo == 0 else os.environ.get("B200DP_AR_STAGE_MB", "8")
+            floor_mb = "1" if algo == 0 else os.environ.get("B200DP_AR_STAGE_MB", "2")
             src_bytes = max(src_bytes_needed, int(floor_mb) << 20)
             src_bytes = (src_bytes + 255) // 256 * 256
-            st = self._ar["stages"][algo] = {
+            st = ch["stages"][algo] = {
                 "src_bytes": src_bytes,
                 "stage": self._region(2 * self.world_size * src_bytes)}
             torch.cuda.synchronize(self.device)
             self.host_barrier()
-        return dict(self._ar, **st)
+        return dict(ch, **st)
+
+    def rs_target(self, nbytes: int, channel: int):
+        """Where a producer kernel may scatter a bucket of `nbytes` directly (fused GEMM
+        epilogue): the two-shot staging of `channel`. Returns the arguments of
+        b200_gemm_bf16_rs."""
+        nvec = nbytes // 16
+        sl = (nvec + self.world_size - 1) // self.world_size
+        ch = self._ar_channel(1, sl * 16, channel)
+        return {"comm": self._blob, "stage_off": ch["stage"], "src_bytes": ch["src_bytes"],
+                "slice_vec": sl, "seq": ch["seq"]}
 
     def choose_algo(self, nbytes: int) -> int:
         """Measured crossover (profiles/allreduce_sweep.md): the tagged one-shot wins while the
@@ -352,7 +368,7 @@ class PeerComm(BaseComm):
         return 0 if nbytes * max(1, self.world_size - 1) <= budget else 1
 
     def all_reduce(self, tensor: torch.Tensor, op: str = "mean", algo="auto", blocks: int = 0,
-                   sgd=None):
+                   sgd=None, channel: int = 0, push_from: int = 0):
         """In-place all-reduce of a contiguous fp32/bf16 tensor whose byte size is a multiple
         of 16. algo: "auto" | "oneshot" | "twoshot". sgd=(master, momentum, hp) fuses the
         SGD-momentum update: `tensor` is then the gradient bucket and the destination is
@@ -369,7 +385,7 @@ class PeerComm(BaseComm):
         W = self.world_size
         nvec = nbytes // 16
         need = 2 * nbytes if a == 0 else ((nvec + W - 1) // W) * 16   # one-shot stages tagged words
-        ch = self._ar_channel(a, need)
+        ch = self._ar_channel(a, need, channel)
         scale = 1.0 / W if op == "mean" else 1.0
         if sgd is None:
             out_t = tensor
@@ -388,7 +404,7 @@ class PeerComm(BaseComm):
             self._blob, _DTYPE_CODE[tensor.dtype], a, upd, tensor.data_ptr(), out_t.data_ptr(),
             out_off or 0, nbytes, ch["stage"], ch["src_bytes"], ch["flags"], self.GMAX, ch["seq"],
             ch["arrive"], scale, N.ptr(master), N.ptr(mom), N.ptr(hp), int(state_base), int(blocks),
-            N.stream()), "b200_comm_allreduce")
+            int(push_from), N.stream()), "b200_comm_allreduce")
         if copy_back is not None:
             out_t.copy_(copy_back[:nbytes].view(out_t.dtype).view(out_t.shape))
         return out_t

@@ -102,6 +102,15 @@ class DataParallel(nn.Module):
         """Slot of parameter i inside the flat gradient bucket."""
         return self._grad_views[i]
 
+    def rs_target(self, i: int):
+        """Fused GEMM -> reduce-scatter target for parameter i's gradient, or None."""
+        if not (self._require_backward_sync and self._pass_open):
+            return None
+        return self.reducer.rs_target(i)
+
+    def mark_pushed(self, target):
+        self.reducer.mark_pushed(target)
+
     def ready(self, i: int):
         """Parameter i's gradient is final in its slot (called from a layer's backward)."""
         if not (self._require_backward_sync and self._pass_open):

@@ -15,6 +15,7 @@ and copies the means back before `optimizer.step()`. This reducer keeps that con
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import List, Optional, Sequence
 
 import torch
@@ -134,6 +135,9 @@ class Reducer:
         self.launched: List[int] = []
         self.sync_enabled = True
         self.kernel_launches = 0
+        self.pushed = {}        # bucket -> vectors already scattered by a fused GEMM epilogue
+        # let wgrad GEMMs scatter straight into the owners' staging (B200DP_FUSE_RS=0 disables)
+        self.fuse_rs = os.environ.get("B200DP_FUSE_RS", "1") != "0"
         if self.fuse:
             lr, mu, wd = fuse_sgd
             dev = flat.param.device
@@ -173,6 +177,32 @@ class Reducer:
     def prepare_for_backward(self):
         self.core.reset()
         self.launched = []
+        self.pushed = {}
+
+    def rs_target(self, param_index: int):
+        """If parameter i's gradient may be scattered to the owner ranks by the GEMM that
+        produces it (fused GEMM -> reduce-scatter), return the b200_gemm_bf16_rs arguments.
+        Conditions: CUDA, world > 1, two-shot algorithm, and the parameter sits at the start
+        of its bucket with a whole number of 16-byte vectors."""
+        if not (self.fuse_rs and self.is_cuda and self.sync_enabled and self.comm.world_size > 1
+                and hasattr(self.comm, "rs_target")):
+            return None
+        b = self.bucket_of[param_index]
+        lo, hi = self.ranges[b]
+        slot = self.flat.slots[param_index]
+        esz = self.flat.grad.element_size()
+        nbytes = (hi - lo) * esz
+        if slot.offset != lo or (slot.numel * esz) % 16 or self._algo_for(nbytes) != 1 \
+                or self.flat.grad.dtype != torch.bfloat16:
+            return None
+        t = dict(self.comm.rs_target(nbytes, channel=b + 1))
+        t["base_vec"] = 0
+        t["_bucket"] = b
+        t["_vecs"] = slot.numel * esz // 16
+        return t
+
+    def mark_pushed(self, target: dict):
+        self.pushed[target["_bucket"]] = target["_vecs"]
 
     def mark_ready(self, param_index: int):
         """Called when parameter i's gradient is final (autograd hook or layer backward)."""
@@ -199,10 +229,14 @@ class Reducer:
         with ctx:
             if self.fuse and self.is_cuda:
                 master, mom, base = self.state[b]
-                self.comm.all_reduce(g, op="mean", algo=algo,
+                self.comm.all_reduce(g, op="mean", algo=algo, channel=b + 1,
+                                     push_from=self.pushed.get(b, 0),
                                      sgd=(self.flat.param[lo:hi], master, mom, self.hp, base))
+            elif self.is_cuda:
+                self.comm.all_reduce(g, op="mean", algo=algo, channel=b + 1,
+                                     push_from=self.pushed.get(b, 0))
             else:
-                self.comm.all_reduce(g, op="mean", algo=algo if self.is_cuda else "auto")
+                self.comm.all_reduce(g, op="mean", algo="auto")
                 if self.fuse:   # CPU/gloo path: plain SGD on the averaged bucket
                     master, mom, _ = self.state[b]
                     lr, mu, wd, _n = self.hp.tolist()

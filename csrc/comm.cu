@@ -396,6 +396,8 @@ struct AllreduceArgs {
   float* mom;             // fp32 momentum of the same elements
   const float* hp;        // {lr, momentum, weight_decay, nesterov}
   size_t state_base;      // element index (in the bucket) that master[0]/mom[0] correspond to
+  size_t push_from;       // ALGO 1: vectors below this index were already scattered to their
+                          // owners by the producing GEMM's epilogue (b200_gemm_bf16_rs)
 };
 
 template <typename T> struct Vec;
@@ -543,7 +545,11 @@ __global__ void __launch_bounds__(AR_THREADS) allreduce_kernel(CommDev c, Allred
       const size_t lim = min(shi, a.nvec > base ? a.nvec - base : 0);
       uint4* dst = peer_ptr<uint4>(c, o, a.stage_off) + slot * slot_vec + (size_t)c.rank * a.src_vec;
       const uint4* src = a.in + base;
-      for (size_t v = slo + threadIdx.x; v < lim; v += 4 * (size_t)nt) {
+      // vectors with bucket index < push_from are already in place (fused GEMM epilogue)
+      const size_t skip = a.push_from > base ? a.push_from - base : 0;
+      size_t v0 = slo + threadIdx.x;
+      if (v0 < skip) v0 += ((skip - v0 + nt - 1) / nt) * nt;
+      for (size_t v = v0; v < lim; v += 4 * (size_t)nt) {
         uint4 x[4];
 #pragma unroll
         for (int u = 0; u < 4; ++u)
@@ -741,9 +747,11 @@ int b200_comm_allreduce(const void* comm, int dtype, int algo, int update, const
                         void* out_local, size_t out_off, size_t bytes, size_t stage_off,
                         size_t src_bytes, size_t flag_off, int gmax, unsigned* seq_ctr,
                         unsigned* arrive_ctr, float scale, float* master, float* mom,
-                        const float* hp, size_t state_base, int blocks, void* stream) {
+                        const float* hp, size_t state_base, int blocks, size_t push_from,
+                        void* stream) {
   const CommDev& c = *(const CommDev*)comm;
   B200_REQUIRE(bytes > 0 && bytes % 16 == 0, "b200_comm_allreduce: size must be a multiple of 16 B");
+  B200_REQUIRE(push_from == 0 || algo == 1, "b200_comm_allreduce: push_from needs the two-shot algorithm");
   B200_REQUIRE(src_bytes % 16 == 0 && stage_off % 16 == 0 && out_off % 16 == 0,
                "b200_comm_allreduce: 16-byte alignment");
   AllreduceArgs a;
@@ -762,6 +770,7 @@ int b200_comm_allreduce(const void* comm, int dtype, int algo, int update, const
   a.mom = mom;
   a.hp = hp;
   a.state_base = state_base;
+  a.push_from = push_from;
   // one-shot stages tagged words (2x the payload); two-shot stages one slice per source
   const size_t need = (algo == 0) ? 2 * a.nvec : (a.nvec + c.world - 1) / c.world;
   B200_REQUIRE(need <= a.src_vec, "b200_comm_allreduce: %zu B per source exceed the staging (%zu B)",

@@ -28,7 +28,7 @@
 #include <mutex>
 #include <unordered_map>
 
-#include "common.cuh"
+#include "comm.cuh"
 
 namespace {
 
@@ -172,6 +172,17 @@ struct GemmParams {
   int relu;
   const __nv_bfloat16* relu_mask;  // [M, ld_mask] or null: output zeroed where mask <= 0
   int ld_mask;
+  // Fused reduce-scatter (wgrad of a data-parallel layer): instead of storing the tile to
+  // C, the epilogue stores every 16-byte vector straight into the staging slot of the rank
+  // that OWNS that slice of the gradient bucket (two-shot all-reduce, csrc/comm.cu), over
+  // NVLink peer memory, while other tiles are still in their main loop.
+  int rs_on;
+  CommDev rs_comm;
+  size_t rs_stage_off;   // arena offset of the bucket's staging [2][world][src_vec]
+  size_t rs_src_vec;     // vectors reserved per source rank in one slot
+  size_t rs_sl;          // vectors per owner slice
+  size_t rs_base_vec;    // vector index of C[0][0] inside the bucket
+  const unsigned* rs_seq;  // the bucket channel's sequence counter (slot = (seq+1) & 1)
 };
 
 template <int BN, bool B_MN> struct Cfg {
@@ -199,7 +210,18 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
+  // With the reduce-scatter epilogue consecutive row tiles belong to different owner ranks
+  // (owner = bucket vector / slice), so a row-major tile order would send all remote traffic
+  // in one burst. Interleave: CTA row y handles tile (y % world) * tiles_per_owner + y / world,
+  // which spreads NVLink stores evenly over the kernel's lifetime.
+  int tile_y = blockIdx.y;
+  if (p.rs_on) {
+    const int W = p.rs_comm.world, T = gridDim.y;
+    const int per = (T + W - 1) / W;
+    const int cand = (tile_y % W) * per + tile_y / W;
+    if (T % W == 0) tile_y = cand;
+  }
+  const int m0 = tile_y * BM, n0 = blockIdx.x * BN;
   const int num_kb = (p.K + BK - 1) / BK;
 
   if (warp == 0 && lane == 0) {
@@ -271,52 +293,59 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
     }
   } else {
     // ===== epilogue: warps 2..5, TMEM lane group = warp % 4 =====
+    // Accumulator rows arrive one per lane (tcgen05.ld 32x32b). Bias / ReLU / mask are applied
+    // in registers. bf16 results are then staged through shared memory (the tile ring is free
+    // once tmem_full has fired) so each warp writes whole 16-byte-vector rows: a store
+    // instruction covers 512 contiguous bytes instead of 32 scattered 16-byte pieces. That
+    // matters most for the reduce-scatter epilogue, whose stores cross NVLink.
     const int lg = warp & 3;
     mbar_wait(tmem_full, 0);
     tcgen05_fence_after();
     const int row = m0 + lg * 32 + lane;
     const bool row_ok = row < p.M;
     constexpr int CHUNK = BN >= 32 ? 32 : 16;
+    constexpr int PITCH = BN * 2 + 16;                       // bytes per staged row
+    uint8_t* sbuf = tiles + lg * (32 * PITCH);
 #pragma unroll 1
     for (int c0 = 0; c0 < BN; c0 += CHUNK) {
       uint32_t r[CHUNK];
       const uint32_t taddr = tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)c0;
       if constexpr (CHUNK == 32) tmem_ld32(taddr, r); else tmem_ld16(taddr, r);
       tmem_ld_wait();
-      if (row_ok) {
-        const int col0 = n0 + c0;
-        float v[CHUNK];
+      const int col0 = n0 + c0;
+      float v[CHUNK];
 #pragma unroll
-        for (int j = 0; j < CHUNK; ++j) v[j] = __uint_as_float(r[j]);
-        if (p.bias) {
+      for (int j = 0; j < CHUNK; ++j) v[j] = __uint_as_float(r[j]);
+      if (p.bias) {
+#pragma unroll
+        for (int j = 0; j < CHUNK; ++j)
+          if (col0 + j < p.N) v[j] += __bfloat162float(p.bias[col0 + j]);
+      }
+      if (p.relu) {
+#pragma unroll
+        for (int j = 0; j < CHUNK; ++j) v[j] = fmaxf(v[j], 0.0f);
+      }
+      if (p.relu_mask && row_ok) {
+        const __nv_bfloat16* mrow = p.relu_mask + (size_t)row * p.ld_mask + col0;
+        if (col0 + CHUNK <= p.N && (p.ld_mask % 8) == 0) {
+#pragma unroll
+          for (int j = 0; j < CHUNK; j += 8) {
+            const uint4 mv = *reinterpret_cast<const uint4*>(mrow + j);
+            const uint32_t w[4] = {mv.x, mv.y, mv.z, mv.w};
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              if (__uint_as_float(w[q] << 16) <= 0.0f) v[j + 2 * q] = 0.0f;
+              if (__uint_as_float(w[q] & 0xffff0000u) <= 0.0f) v[j + 2 * q + 1] = 0.0f;
+            }
+          }
+        } else {
 #pragma unroll
           for (int j = 0; j < CHUNK; ++j)
-            if (col0 + j < p.N) v[j] += __bfloat162float(p.bias[col0 + j]);
+            if (col0 + j < p.N && __bfloat162float(mrow[j]) <= 0.0f) v[j] = 0.0f;
         }
-        if (p.relu) {
-#pragma unroll
-          for (int j = 0; j < CHUNK; ++j) v[j] = fmaxf(v[j], 0.0f);
-        }
-        if (p.relu_mask) {
-          const __nv_bfloat16* mrow = p.relu_mask + (size_t)row * p.ld_mask + col0;
-          if (col0 + CHUNK <= p.N && (p.ld_mask % 8) == 0) {
-#pragma unroll
-            for (int j = 0; j < CHUNK; j += 8) {
-              const uint4 mv = *reinterpret_cast<const uint4*>(mrow + j);
-              const uint32_t w[4] = {mv.x, mv.y, mv.z, mv.w};
-#pragma unroll
-              for (int q = 0; q < 4; ++q) {
-                if (__uint_as_float(w[q] << 16) <= 0.0f) v[j + 2 * q] = 0.0f;
-                if (__uint_as_float(w[q] & 0xffff0000u) <= 0.0f) v[j + 2 * q + 1] = 0.0f;
-              }
-            }
-          } else {
-#pragma unroll
-            for (int j = 0; j < CHUNK; ++j)
-              if (col0 + j < p.N && __bfloat162float(mrow[j]) <= 0.0f) v[j] = 0.0f;
-          }
-        }
-        if (p.c_fp32) {
+      }
+      if (p.c_fp32) {
+        if (row_ok) {
           float* crow = reinterpret_cast<float*>(p.C) + (size_t)row * p.ldc + col0;
           if (col0 + CHUNK <= p.N && (p.ldc % 4) == 0) {
 #pragma unroll
@@ -327,23 +356,58 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
             for (int j = 0; j < CHUNK; ++j)
               if (col0 + j < p.N) crow[j] = v[j];
           }
+        }
+      } else {
+        // pack to bf16 and park this lane's row segment in shared memory
+#pragma unroll
+        for (int j = 0; j < CHUNK; j += 8) {
+          uint32_t w[4];
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const __nv_bfloat162 h = __floats2bfloat162_rn(v[j + 2 * q], v[j + 2 * q + 1]);
+            w[q] = *reinterpret_cast<const uint32_t*>(&h);
+          }
+          *reinterpret_cast<uint4*>(sbuf + lane * PITCH + (c0 + j) * 2) = make_uint4(w[0], w[1], w[2], w[3]);
+        }
+      }
+    }
+    if (!p.c_fp32) {
+      __syncwarp();
+      constexpr int VPR = BN / 8;                   // 16-byte vectors per tile row
+      constexpr int RPI = 32 / VPR;                 // rows written per warp-wide store
+      const int cv = lane % VPR;
+      const int col = n0 + cv * 8;
+      const bool vec_ok = (p.ldc % 8) == 0 && ((reinterpret_cast<uintptr_t>(p.C) & 15) == 0);
+      unsigned slot = 0;
+      size_t slot_vec = 0;
+      if (p.rs_on) {
+        slot = (*p.rs_seq + 1u) & 1u;
+        slot_vec = (size_t)p.rs_comm.world * p.rs_src_vec;
+      }
+#pragma unroll 1
+      for (int it = 0; it < VPR; ++it) {           // 32 rows / RPI rows per iteration == VPR
+        const int rl = it * RPI + lane / VPR;
+        const int grow = m0 + lg * 32 + rl;
+        if (grow >= p.M || col >= p.N) continue;
+        const uint4 val = *reinterpret_cast<const uint4*>(sbuf + rl * PITCH + cv * 16);
+        if (p.rs_on) {
+          // reduce-scatter epilogue: vector `vec` of the bucket goes to owner vec / sl
+          if (col + 8 <= p.N) {
+            const size_t vec = p.rs_base_vec + ((size_t)grow * p.ldc + col) / 8;
+            const int owner = (int)(vec / p.rs_sl);
+            uint4* dst = peer_ptr<uint4>(p.rs_comm, owner, p.rs_stage_off) + slot * slot_vec +
+                         (size_t)p.rs_comm.rank * p.rs_src_vec + (vec - (size_t)owner * p.rs_sl);
+            *dst = val;
+          }
         } else {
-          __nv_bfloat16* crow = reinterpret_cast<__nv_bfloat16*>(p.C) + (size_t)row * p.ldc + col0;
-          if (col0 + CHUNK <= p.N && (p.ldc % 8) == 0) {
-#pragma unroll
-            for (int j = 0; j < CHUNK; j += 8) {
-              uint32_t w[4];
-#pragma unroll
-              for (int q = 0; q < 4; ++q) {
-                const __nv_bfloat162 h = __floats2bfloat162_rn(v[j + 2 * q], v[j + 2 * q + 1]);
-                w[q] = *reinterpret_cast<const uint32_t*>(&h);
-              }
-              *reinterpret_cast<uint4*>(crow + j) = make_uint4(w[0], w[1], w[2], w[3]);
-            }
+          __nv_bfloat16* cptr = reinterpret_cast<__nv_bfloat16*>(p.C) + (size_t)grow * p.ldc + col;
+          if (vec_ok && col + 8 <= p.N) {
+            *reinterpret_cast<uint4*>(cptr) = val;
           } else {
+            const __nv_bfloat16* sv = reinterpret_cast<const __nv_bfloat16*>(&val);
 #pragma unroll
-            for (int j = 0; j < CHUNK; ++j)
-              if (col0 + j < p.N) crow[j] = __float2bfloat16_rn(v[j]);
+            for (int j = 0; j < 8; ++j)
+              if (col + j < p.N) cptr[j] = sv[j];
           }
         }
       }
@@ -436,9 +500,30 @@ extern "C" {
 //   bias: bf16 [N] or null; relu: clamp at 0; relu_mask: bf16 [M][ld_mask] or null, output is
 //   zeroed where the mask is <= 0 (ReLU backward fused into dgrad).
 // All pitches in elements; operand pitches must be multiples of 8 elements (16 bytes).
+int b200_gemm_bf16_rs(const void* A, int a_mn, long long lda, const void* B, int b_mn,
+                      long long ldb, void* C, int c_fp32, long long ldc, int M, int N, int K,
+                      const void* bias, int relu, const void* relu_mask, long long ld_mask,
+                      const void* rs_comm, size_t rs_stage_off, size_t rs_src_bytes,
+                      size_t rs_slice_vec, size_t rs_base_vec, const unsigned* rs_seq,
+                      void* stream);
+
 int b200_gemm_bf16(const void* A, int a_mn, long long lda, const void* B, int b_mn, long long ldb,
                    void* C, int c_fp32, long long ldc, int M, int N, int K, const void* bias,
                    int relu, const void* relu_mask, long long ld_mask, void* stream) {
+  return b200_gemm_bf16_rs(A, a_mn, lda, B, b_mn, ldb, C, c_fp32, ldc, M, N, K, bias, relu,
+                           relu_mask, ld_mask, nullptr, 0, 0, 0, 0, nullptr, stream);
+}
+
+// Same product with the reduce-scatter epilogue (see GemmParams::rs_*): C is not written;
+// every 16-byte vector of the result lands in the owner rank's staging slot of the bucket's
+// two-shot all-reduce channel. Follow it with b200_comm_allreduce(..., push_from = vectors
+// produced here) on the same channel.
+int b200_gemm_bf16_rs(const void* A, int a_mn, long long lda, const void* B, int b_mn,
+                      long long ldb, void* C, int c_fp32, long long ldc, int M, int N, int K,
+                      const void* bias, int relu, const void* relu_mask, long long ld_mask,
+                      const void* rs_comm, size_t rs_stage_off, size_t rs_src_bytes,
+                      size_t rs_slice_vec, size_t rs_base_vec, const unsigned* rs_seq,
+                      void* stream) {
   B200_REQUIRE(M > 0 && N > 0 && K > 0, "b200_gemm_bf16: empty problem");
   const int BN = (N <= 16) ? 16 : (N <= 32 ? 32 : (N <= 64 ? 64 : 128));
   CUtensorMap ma, mb;
@@ -454,6 +539,18 @@ int b200_gemm_bf16(const void* A, int a_mn, long long lda, const void* B, int b_
   p.relu = relu;
   p.relu_mask = (const __nv_bfloat16*)relu_mask;
   p.ld_mask = (int)ld_mask;
+  p.rs_on = 0;
+  if (rs_comm) {
+    B200_REQUIRE(!c_fp32 && ldc == N && N % 8 == 0 && !bias && !relu && !relu_mask,
+                 "b200_gemm_bf16: the reduce-scatter epilogue needs a dense bf16 [M,N] output, N %% 8 == 0");
+    p.rs_on = 1;
+    memcpy(&p.rs_comm, rs_comm, sizeof(CommDev));
+    p.rs_stage_off = rs_stage_off;
+    p.rs_src_vec = rs_src_bytes / 16;
+    p.rs_sl = rs_slice_vec;
+    p.rs_base_vec = rs_base_vec;
+    p.rs_seq = rs_seq;
+  }
   cudaStream_t s = (cudaStream_t)stream;
   switch (BN) {
     case 16: return dispatch_major<16>(a_mn, b_mn, ma, mb, p, s);

@@ -151,7 +151,42 @@ int b200_comm_allreduce(const void* comm, int dtype, int algo, int update, const
                         void* out_local, size_t out_off, size_t bytes, size_t stage_off,
                         size_t src_bytes, size_t flag_off, int gmax, unsigned* seq_ctr,
                         unsigned* arrive_ctr, float scale, float* master, float* mom,
-                        const float* hp, size_t state_base, int blocks, void* stream);
+                        const float* hp, size_t state_base, int blocks, size_t push_from,
+                        void* stream);
+
+/* ---- tcgen05 bf16 GEMM ------------------------------------------------------------------ */
+/* C[M,N] = op(A) op(B)^T, fp32 accumulation in TMEM. a_mn/b_mn select MN-major operands, so
+ * forward, dgrad and wgrad of a linear layer need no transposes. Ref: nn.Linear layers of
+ * src/model.py:12-13 widened per BASELINE.json config 4. */
+int b200_gemm_bf16(const void* A, int a_mn, long long lda, const void* B, int b_mn, long long ldb,
+                   void* C, int c_fp32, long long ldc, int M, int N, int K, const void* bias,
+                   int relu, const void* relu_mask, long long ld_mask, void* stream);
+/* Same product with a fused reduce-scatter epilogue: result vectors go straight to the owner
+ * ranks' staging of a two-shot all-reduce channel over NVLink peer memory. */
+int b200_gemm_bf16_rs(const void* A, int a_mn, long long lda, const void* B, int b_mn,
+                      long long ldb, void* C, int c_fp32, long long ldc, int M, int N, int K,
+                      const void* bias, int relu, const void* relu_mask, long long ld_mask,
+                      const void* rs_comm, size_t rs_stage_off, size_t rs_src_bytes,
+                      size_t rs_slice_vec, size_t rs_base_vec, const unsigned* rs_seq,
+                      void* stream);
+/* conv2 forward as a TF32 implicit GEMM on tcgen05 (same contract as b200_conv2_fwd). */
+int b200_conv2_fwd_tc(const float* a1, const float* w, const float* b, float* mask, int mask_mode,
+                      float p, unsigned long long seed, unsigned long long step, float* a2,
+                      void* pos2, int B, void* stream);
+/* MLP helpers: fused softmax + NLL + gradient, bias gradient, master-weight SGD. */
+int b200_softmax_nll_bf16(const float* logits, int ld, int ncls, const long long* labels,
+                          float* loss, void* dlogits, int ld_d, int B, void* stream);
+int b200_colsum_bf16(const void* dy, long long ld, void* out, int B, int N, void* stream);
+int b200_sgd_master_bf16(void* p, const void* g, float* master, float* mom, long long n,
+                         const float* hp, void* stream);
+/* Native step runner (pinned host -> device streaming of the fused step). */
+int b200_runner_config_size(void);
+int b200_runner_create(const void* cfg_blob, void** out);
+int b200_runner_run(void* h, const void* hx, const long long* hy, int steps, float* hloss,
+                    void* caller_stream);
+int b200_runner_destroy(void* h);
+int b200_pdl_enabled(void);
+int b200_net_set_phase_debug(long long* buf);
 
 /* ---- bucket planner + reducer core (host only) --------------------------------------- */
 /* Ref: torch DDP's bucket rule reached from src/train_dist.py:63 */
