@@ -42,6 +42,14 @@ N.register_sigs({
     "b200_comm_send": [c_p, c_i, c_p, c_sz, c_sz, c_sz, c_sz, c_sz, c_p, c_p],
     "b200_comm_recv": [c_p, c_i, c_p, c_sz, c_sz, c_sz, c_sz, c_sz, c_p, c_p],
     "b200_comm_sendrecv": [c_p, c_i, c_p, c_sz, c_i, c_p, c_sz, c_sz, c_sz, c_sz, c_sz, c_p, c_p, c_p],
+    "b200_nvls_supported": [c_i, C.POINTER(c_i)],
+    "b200_nvls_granularity": [c_i, c_sz, C.POINTER(c_sz)],
+    "b200_nvls_create": [c_i, c_sz, C.POINTER(c_ull), C.POINTER(c_i)],
+    "b200_nvls_import": [c_i, C.POINTER(c_ull)],
+    "b200_nvls_add_device": [c_ull, c_i],
+    "b200_nvls_bind_map": [c_ull, c_i, c_sz, C.POINTER(c_p), C.POINTER(c_p)],
+    "b200_nvls_allreduce": [c_p, c_p, c_sz, c_sz, c_i, c_sz, c_i, c_p, c_p, c_f, c_i, c_sz, c_p, c_p,
+                            c_p, c_sz, c_i, c_p],
     "b200_comm_net_stage_bytes": [],
     "b200_comm_net_flag_bytes": [],
     "b200_comm_net_reduce_allreduce_sgd": [c_p, c_p, c_i, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_p,
@@ -192,6 +200,7 @@ class PeerComm(BaseComm):
         self._p2p_acks = self._region(MAX_WORLD * 4)
         self._sent = torch.zeros(MAX_WORLD, dtype=torch.int32, device=self.device)
         self._recvd = torch.zeros(MAX_WORLD, dtype=torch.int32, device=self.device)
+        self._nvls = None     # lazily: NVLS (multicast) region, False if unsupported
         self._net = None      # lazily: staging/flags of the fused Net kernel B
         self._ar = None       # lazily: generic all-reduce channel
         self._bounce: Dict[int, torch.Tensor] = {}
@@ -237,7 +246,9 @@ class PeerComm(BaseComm):
         if e[0] != 0:
             where = {1: "barrier", 2: "broadcast(root waits)", 3: "broadcast(wait root)",
                      4: "send(wait ack)", 5: "recv", 6: "net all-reduce", 7: "one-shot all-reduce",
-                     8: "two-shot reduce-scatter", 9: "two-shot all-gather"}.get(e[2], str(e[2]))
+                     8: "two-shot reduce-scatter", 9: "two-shot all-gather",
+                     10: "NVLS all-reduce (inputs ready)", 11: "NVLS all-reduce (results)"
+                     }.get(e[2], str(e[2]))
             raise CommError(f"rank {self.rank}: timed out waiting for rank {e[1]} in {where} "
                             f"(sequence {e[3] & 0xffffffff})")
 
@@ -320,6 +331,99 @@ class PeerComm(BaseComm):
             tmp[:nbytes].copy_(tensor.contiguous().view(-1).view(torch.uint8))
         return tmp, pad
 
+    # -- NVLS (NVLink SHARP): multicast region ---------------------------------------
+    def nvls_init(self, nbytes: Optional[int] = None) -> bool:
+        """Create the multicast object and this rank's bound memory (once). Returns False if
+        the driver / fabric does not offer multicast on every rank (callers fall back to the
+        two-shot kernel). Collective: every rank must call it at the same point."""
+        if self._nvls is not None:
+            return bool(self._nvls)
+        import socket
+        lib = self.lib
+        ok = c_i(0)
+        rc = lib.b200_nvls_supported(self.device.index or 0, C.byref(ok))
+        mine = (rc == 0 and ok.value == 1 and self.world_size > 1
+                and os.environ.get("B200DP_NVLS", "1") != "0")
+        if not all(self.all_gather_object(bool(mine))):
+            self._nvls = False
+            return False
+        nbytes = nbytes or (int(os.environ.get("B200DP_NVLS_MB", "128")) << 20)
+        rounded = c_sz(0)
+        N.check(lib.b200_nvls_granularity(self.world_size, nbytes, C.byref(rounded)),
+                "b200_nvls_granularity")
+        mc = c_ull(0)
+        path = f"/tmp/b200dp_nvls_{os.environ.get('MASTER_PORT', '0')}_{os.getuid()}_{id(self) & 0xffff}"
+        path = self.all_gather_object(path)[0]
+        status = "ok"
+        try:
+            if self.rank == 0:
+                fd = c_i(-1)
+                N.check(lib.b200_nvls_create(self.world_size, rounded.value, C.byref(mc),
+                                             C.byref(fd)), "b200_nvls_create")
+                if os.path.exists(path):
+                    os.unlink(path)
+                srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+                srv.bind(path)
+                srv.listen(self.world_size)
+                self.host_barrier()
+                for _ in range(self.world_size - 1):
+                    conn, _a = srv.accept()
+                    socket.send_fds(conn, [b"mc"], [fd.value])
+                    conn.close()
+                srv.close()
+                os.unlink(path)
+                os.close(fd.value)
+            else:
+                self.host_barrier()
+                cl = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+                cl.connect(path)
+                _msg, fds, _f, _a = socket.recv_fds(cl, 16, 1)
+                cl.close()
+                N.check(lib.b200_nvls_import(fds[0], C.byref(mc)), "b200_nvls_import")
+                os.close(fds[0])
+            N.check(lib.b200_nvls_add_device(mc.value, self.device.index or 0), "b200_nvls_add_device")
+        except Exception as e:   # keep the ranks in step, then give up together
+            status = f"{type(e).__name__}: {e}"
+        if any(x != "ok" for x in self.all_gather_object(status)):
+            self._nvls = False
+            return False
+        uc, mcp = c_p(), c_p()
+        try:
+            N.check(lib.b200_nvls_bind_map(mc.value, self.device.index or 0, rounded.value,
+                                           C.byref(uc), C.byref(mcp)), "b200_nvls_bind_map")
+        except Exception as e:
+            status = f"{type(e).__name__}: {e}"
+        if any(x != "ok" for x in self.all_gather_object(status)):
+            self._nvls = False
+            return False
+        self._nvls = {"uc": uc.value, "mc": mcp.value, "bytes": rounded.value, "top": 0,
+                      "arena": torch.as_tensor(_RawCudaMemory(uc.value, rounded.value),
+                                               device=self.device)}
+        self.host_barrier()
+        return True
+
+    def alloc_nvls(self, numel: int, dtype=torch.float32, device=None) -> torch.Tensor:
+        """A zeroed tensor inside the NVLS region (same call order on every rank)."""
+        if not self.nvls_init():
+            raise CommError("NVLS is not available on this machine")
+        nv = self._nvls
+        esz = torch.empty((), dtype=dtype).element_size()
+        off = (nv["top"] + 255) // 256 * 256
+        if off + numel * esz > nv["bytes"]:
+            raise CommError("NVLS region exhausted: raise B200DP_NVLS_MB")
+        nv["top"] = off + numel * esz
+        t = nv["arena"][off:off + numel * esz].view(dtype)
+        t.zero_()
+        return t
+
+    def nvls_offset_of(self, t: torch.Tensor) -> Optional[int]:
+        if not self._nvls:
+            return None
+        off = t.data_ptr() - self._nvls["uc"]
+        if 0 <= off and off + t.numel() * t.element_size() <= self._nvls["bytes"]:
+            return off
+        return None
+
     # -- generic all-reduce ----------------------------------------------------
     GMAX = 256
 
@@ -380,6 +484,8 @@ class PeerComm(BaseComm):
         nbytes = tensor.numel() * tensor.element_size()
         if nbytes % 16:
             raise CommError("all_reduce size must be a multiple of 16 bytes (pad the bucket)")
+        if algo == "nvls" or algo == 2:
+            return self._all_reduce_nvls(tensor, op, sgd, channel, blocks)
         a = {"auto": self.choose_algo(nbytes), "oneshot": 0, "twoshot": 1}[algo] \
             if isinstance(algo, str) else int(algo)
         W = self.world_size
@@ -407,6 +513,28 @@ class PeerComm(BaseComm):
             int(push_from), N.stream()), "b200_comm_allreduce")
         if copy_back is not None:
             out_t.copy_(copy_back[:nbytes].view(out_t.dtype).view(out_t.shape))
+        return out_t
+
+    def _all_reduce_nvls(self, tensor, op, sgd, channel, blocks):
+        """In-switch reduction: `tensor` must live in the NVLS region (alloc_nvls)."""
+        off = self.nvls_offset_of(tensor)
+        if off is None:
+            raise CommError("all_reduce(algo='nvls') needs a tensor from comm.alloc_nvls()")
+        nbytes = tensor.numel() * tensor.element_size()
+        ch = self._ar_channel(1, 16, channel)
+        scale = 1.0 / self.world_size if op == "mean" else 1.0
+        if sgd is None:
+            upd, out_off, master, mom, hp, base = 0, 0, None, None, None, 0
+            out_t = tensor
+        else:
+            out_t, master, mom, hp, base = sgd
+            upd, out_off = 1, self.offset_of(out_t)
+            if out_off is None:
+                raise CommError("fused SGD needs the parameters in the symmetric arena")
+        N.check(self.lib.b200_nvls_allreduce(
+            self._blob, self._nvls["mc"], off, nbytes, _DTYPE_CODE[tensor.dtype], ch["flags"],
+            self.GMAX, ch["seq"], ch["arrive"], scale, upd, out_off, N.ptr(master), N.ptr(mom),
+            N.ptr(hp), int(base), int(blocks), N.stream()), "b200_nvls_allreduce")
         return out_t
 
     # -- fused Net kernel B ------------------------------------------------------

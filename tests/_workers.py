@@ -249,3 +249,24 @@ def trainer_dist(rank, world, backend, out_dir):
     torch.save({"param": tr.flat.param.clone().cpu(), "test_losses": log.test_losses,
                 "n_train_losses": len(log.train_losses)}, os.path.join(out_dir, f"tr_{rank}.pt"))
     P.destroy_process_group()
+
+
+def nvls_allreduce(rank, world, backend, out_dir):
+    """In-switch (multimem) all-reduce, fp32 and bf16, twice on the same buffers."""
+    P = _pg()
+    comm = P.init_process_group(backend=backend, rank=rank, world_size=world)
+    dev = comm.device
+    res = {"supported": bool(comm.nvls_init(32 << 20))}
+    if res["supported"]:
+        for name, dtype in (("f32", torch.float32), ("bf16", torch.bfloat16)):
+            for n in (8, 4096 + 8, 1 << 20):
+                t = comm.alloc_nvls(n, dtype)
+                for k, op in enumerate(("mean", "sum")):
+                    g = torch.Generator().manual_seed(100 + rank)
+                    t.copy_(torch.randn(n, generator=g).to(dtype))
+                    comm.all_reduce(t, op=op, algo="nvls")
+                    res[f"{name}_{n}_{op}"] = t.float().cpu().clone()
+        torch.cuda.synchronize()
+        comm.check_errors()
+    torch.save(res, os.path.join(out_dir, f"nvls_{rank}.pt"))
+    P.destroy_process_group()

@@ -107,3 +107,22 @@ def test_trainer_distributed_peer(native_lib, tmp_path):
     # per-rank batch int(64/2) = 32 over a shard of 1036 samples: 33 batches per epoch
     assert res[0]["n_train_losses"] == 2 * 33
     assert (tmp_path / "results" / "model.pt").exists()             # rank 0 only
+
+
+def test_nvls_allreduce_peer(native_lib, tmp_path):
+    """NVLink SHARP: multimem.ld_reduce / multimem.st all-reduce vs the expected sums."""
+    world = _world()
+    launch(_workers.nvls_allreduce, world, args=("b200", str(tmp_path)), timeout=600)
+    res = [torch.load(tmp_path / f"nvls_{r}.pt") for r in range(world)]
+    if not res[0]["supported"]:
+        pytest.skip("multicast (NVLS) is not offered by this driver / fabric")
+    for name, dtype in (("f32", torch.float32), ("bf16", torch.bfloat16)):
+        for n in (8, 4096 + 8, 1 << 20):
+            xs = [torch.randn(n, generator=torch.Generator().manual_seed(100 + r)).to(dtype).float()
+                  for r in range(world)]
+            want = torch.stack(xs).sum(0)
+            tol = dict(rtol=1e-5, atol=1e-5) if name == "f32" else dict(rtol=2e-2, atol=2e-2)
+            for r in range(world):
+                torch.testing.assert_close(res[r][f"{name}_{n}_sum"], want, **tol)
+                torch.testing.assert_close(res[r][f"{name}_{n}_mean"], want / world, **tol)
+                assert torch.equal(res[r][f"{name}_{n}_sum"], res[0][f"{name}_{n}_sum"])
