@@ -27,6 +27,9 @@ from .reducer import Reducer
 class DataParallel(nn.Module):
     def __init__(self, module: nn.Module, comm=None, bucket_of: Optional[Sequence[int]] = None,
                  fuse_sgd=None, algo="auto", broadcast_from: int = 0):
+        """algo: "auto" | "oneshot" | "twoshot" | "nvls". "nvls" places the gradient buckets in
+        the multicast (NVLink SHARP) region so the switch reduces them; it falls back to
+        "twoshot" when the machine does not offer multicast."""
         super().__init__()
         if comm is None:
             from .process_group import get_comm
@@ -34,7 +37,13 @@ class DataParallel(nn.Module):
         self.module = module
         self.comm = comm
         self._verify_shapes()
-        self.flat = FlatParams(module, alloc=comm.alloc)
+        grad_alloc = None
+        if algo == "nvls":
+            if hasattr(comm, "nvls_init") and comm.world_size > 1 and comm.nvls_init():
+                grad_alloc = comm.alloc_nvls
+            else:
+                algo = "twoshot"
+        self.flat = FlatParams(module, alloc=comm.alloc, grad_alloc=grad_alloc)
         # init_sync: rank 0's parameters (and buffers) win (torch DDP default)
         if comm.world_size > 1:
             comm.broadcast(self.flat.param, root=broadcast_from)

@@ -146,7 +146,7 @@ class Reducer:
             self.state = []
             for (lo, hi) in self.ranges:
                 nbytes = (hi - lo) * esz
-                two_shot = self._algo_for(nbytes) == 1 and W > 1
+                two_shot = self._algo_for(nbytes) in (1, 2) and W > 1   # sharded optimizer state
                 if two_shot:   # this rank owns slice r of the bucket: shard master + momentum
                     nvec = nbytes // 16
                     sl = (nvec + W - 1) // W
@@ -168,7 +168,7 @@ class Reducer:
     def _algo_for(self, nbytes: int) -> int:
         if self.algo == "auto":
             return self.comm.choose_algo(nbytes) if hasattr(self.comm, "choose_algo") else 0
-        return {"oneshot": 0, "twoshot": 1}[self.algo]
+        return {"oneshot": 0, "twoshot": 1, "nvls": 2}[self.algo]
 
     def set_lr(self, lr: float):
         self.hp[0] = lr

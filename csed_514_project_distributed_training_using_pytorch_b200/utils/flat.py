@@ -52,7 +52,7 @@ class FlatParams:
     """
 
     def __init__(self, module: nn.Module, alloc: Optional[Callable] = None,
-                 with_momentum: bool = True):
+                 with_momentum: bool = True, grad_alloc: Optional[Callable] = None):
         params = [(n, p) for n, p in module.named_parameters()]
         if not params:
             raise ValueError("module has no parameters")
@@ -67,7 +67,7 @@ class FlatParams:
                                              elem_size=params[0][1].element_size())
         alloc = alloc or (lambda n, dtype, device: torch.zeros(n, dtype=dtype, device=device))
         self.param = alloc(self.numel, dt, dev)
-        self.grad = alloc(self.numel, dt, dev)
+        self.grad = (grad_alloc or alloc)(self.numel, dt, dev)
         self.momentum = alloc(self.numel, torch.float32 if dt != torch.float32 else dt, dev) \
             if with_momentum else None
         self.param.zero_()

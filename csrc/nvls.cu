@@ -120,55 +120,77 @@ __global__ void __launch_bounds__(512) nvls_allreduce_kernel(CommDev c, NvlsArgs
   const size_t lim = min(min(sl, slo + sub), a.nvec > mybase ? a.nvec - mybase : 0);
   char* mc = a.mc_base + a.buf_off;
   const int N = a.bf16 ? 8 : 4;
-  for (size_t v = slo + threadIdx.x; v < lim; v += nt) {
-    const size_t gv = mybase + v;
-    uint4 x = a.bf16 ? mm_ld_reduce_bf16(mc + gv * 16) : mm_ld_reduce_f32(mc + gv * 16);
-    float f[8];
-    if (a.bf16) {
-      const unsigned w[4] = {x.x, x.y, x.z, x.w};
+  // 4 switch reductions in flight per thread: multimem.ld_reduce is a round trip through the
+  // NVSwitch, so bandwidth needs depth.
+  for (size_t v0 = slo + threadIdx.x; v0 < lim; v0 += 4 * (size_t)nt) {
+    uint4 x[4];
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        f[2 * i] = __uint_as_float(w[i] << 16);
-        f[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
-      }
-    } else {
-      f[0] = __uint_as_float(x.x); f[1] = __uint_as_float(x.y);
-      f[2] = __uint_as_float(x.z); f[3] = __uint_as_float(x.w);
+    for (int u = 0; u < 4; ++u) {
+      const size_t v = v0 + (size_t)u * nt;
+      if (v < lim)
+        x[u] = a.bf16 ? mm_ld_reduce_bf16(mc + (mybase + v) * 16) : mm_ld_reduce_f32(mc + (mybase + v) * 16);
     }
-    for (int i = 0; i < N; ++i) f[i] *= a.scale;
-    if (a.update) {
-      const float lr = a.hp[0], mu = a.hp[1], wd = a.hp[2];
-      const size_t e0 = gv * N - a.state_base;
-      for (int i = 0; i < N; ++i) {
-        float w = a.master[e0 + i];
-        const float g = f[i] + wd * w;
-        const float m = mu * a.mom[e0 + i] + g;
-        a.mom[e0 + i] = m;
-        w -= lr * m;
-        a.master[e0 + i] = w;
-        f[i] = w;
-      }
-    }
-    uint4 o;
-    if (a.bf16) {
-      unsigned w[4];
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const __nv_bfloat162 h = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
-        w[i] = *reinterpret_cast<const unsigned*>(&h);
+    for (int u = 0; u < 4; ++u) {
+      const size_t v = v0 + (size_t)u * nt;
+      if (v >= lim) continue;
+      const size_t gv = mybase + v;
+      float f[8];
+      if (a.bf16) {
+        const unsigned w[4] = {x[u].x, x[u].y, x[u].z, x[u].w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          f[2 * i] = __uint_as_float(w[i] << 16);
+          f[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+        }
+      } else {
+        f[0] = __uint_as_float(x[u].x); f[1] = __uint_as_float(x[u].y);
+        f[2] = __uint_as_float(x[u].z); f[3] = __uint_as_float(x[u].w);
+        f[4] = f[5] = f[6] = f[7] = 0.0f;
       }
-      o = make_uint4(w[0], w[1], w[2], w[3]);
-    } else {
-      o = make_uint4(__float_as_uint(f[0]), __float_as_uint(f[1]), __float_as_uint(f[2]),
-                     __float_as_uint(f[3]));
-    }
-    if (a.update) {
-      for (int pp = 0; pp < W; ++pp) {
-        const int p = (c.rank + pp) % W;
-        peer_ptr<uint4>(c, p, a.out_off)[gv] = o;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) f[i] *= a.scale;
+      if (a.update) {
+        const float lr = a.hp[0], mu = a.hp[1], wd = a.hp[2];
+        const size_t e0 = gv * N - a.state_base;      // multiple of N: 16-byte aligned state
+        float4* mw = reinterpret_cast<float4*>(a.master + e0);
+        float4* mb = reinterpret_cast<float4*>(a.mom + e0);
+        for (int q = 0; q < N / 4; ++q) {
+          float4 w = mw[q], m = mb[q];
+          float* wp = reinterpret_cast<float*>(&w);
+          float* bp = reinterpret_cast<float*>(&m);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const float g = f[4 * q + i] + wd * wp[i];
+            bp[i] = mu * bp[i] + g;
+            wp[i] -= lr * bp[i];
+            f[4 * q + i] = wp[i];
+          }
+          mw[q] = w;
+          mb[q] = m;
+        }
       }
-    } else {
-      mm_st(mc + gv * 16, o);   // one store, the switch replicates it to every rank
+      uint4 o;
+      if (a.bf16) {
+        unsigned w[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const __nv_bfloat162 h = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+          w[i] = *reinterpret_cast<const unsigned*>(&h);
+        }
+        o = make_uint4(w[0], w[1], w[2], w[3]);
+      } else {
+        o = make_uint4(__float_as_uint(f[0]), __float_as_uint(f[1]), __float_as_uint(f[2]),
+                       __float_as_uint(f[3]));
+      }
+      if (a.update) {
+        for (int pp = 0; pp < W; ++pp) {
+          const int p = (c.rank + pp) % W;
+          peer_ptr<uint4>(c, p, a.out_off)[gv] = o;
+        }
+      } else {
+        mm_st(mc + gv * 16, o);   // one store, the switch replicates it to every rank
+      }
     }
   }
   __threadfence_system();

@@ -20,6 +20,7 @@ ap.add_argument("--batch", type=int, default=512)
 ap.add_argument("--steps", type=int, default=50)
 ap.add_argument("--warmup", type=int, default=10)
 ap.add_argument("--skip-torch", action="store_true")
+ap.add_argument("--algo", default="twoshot", choices=["twoshot", "nvls", "oneshot", "auto"])
 a = ap.parse_args()
 rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
 torch.cuda.set_device(local)
@@ -30,7 +31,7 @@ B = a.batch
 g = torch.Generator().manual_seed(rank)
 x = torch.randn(B, 784, generator=g).to(torch.bfloat16).to(dev)
 y = torch.randint(0, 10, (B,), generator=g).to(dev)
-out = {"world": world, "per_gpu_batch": B, "grad_bytes_bf16": 20037642 * 2}
+out = {"world": world, "per_gpu_batch": B, "grad_bytes_bf16": 20037642 * 2, "algo": a.algo}
 
 
 def timed(fn, steps, warm):
@@ -50,7 +51,7 @@ def timed(fn, steps, warm):
 torch.manual_seed(0)
 model = WideMLP().to(dev)
 if comm is not None:
-    ddp = DataParallel(model, comm, bucket_of=[2, 2, 1, 1, 0, 0], fuse_sgd=(0.02, 0.5, 0.0), algo="twoshot")
+    ddp = DataParallel(model, comm, bucket_of=[2, 2, 1, 1, 0, 0], fuse_sgd=(0.02, 0.5, 0.0), algo=a.algo)
     def ours_step():
         ddp.loss(x, y).backward()
     def ours_sync():

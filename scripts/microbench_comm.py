@@ -71,9 +71,14 @@ def main():
                 if nbytes <= (4 << 20):
                     row["oneshot_us"] = timed(comm, lambda: comm.all_reduce(t, "sum", "oneshot"), iters)
                 row["twoshot_us"] = timed(comm, lambda: comm.all_reduce(t, "sum", "twoshot"), iters)
+            if comm.nvls_init(300 << 20) and nbytes <= (256 << 20):
+                if "nv" not in globals():
+                    globals()["nv"] = comm.alloc_nvls((256 << 20) // 4, torch.float32)
+                tn = globals()["nv"][:n]
+                row["nvls_us"] = timed(comm, lambda: comm.all_reduce(tn, "sum", "nvls"), iters)
             x = torch.randn(n, device=dev)
             row["nccl_us"] = timed(comm, lambda: dist.all_reduce(x), iters)
-            for k in ("oneshot_us", "twoshot_us", "nccl_us"):
+            for k in ("oneshot_us", "twoshot_us", "nvls_us", "nccl_us"):
                 if k in row:   # bus bandwidth = 2(N-1)/N * S / t
                     row[k.replace("_us", "_busGBs")] = 2 * (world - 1) / world * nbytes / (row[k] * 1e-6) / 1e9
             rows.append(row)
@@ -82,7 +87,8 @@ def main():
         from csed_514_project_distributed_training_using_pytorch_b200.models.mlp import WideMLP
         torch.manual_seed(0)
         model = WideMLP().to(dev)
-        ddp = DataParallel(model, comm, bucket_of=[2, 2, 1, 1, 0, 0], fuse_sgd=(0.02, 0.5, 0.0), algo="twoshot")
+        ddp = DataParallel(model, comm, bucket_of=[2, 2, 1, 1, 0, 0], fuse_sgd=(0.02, 0.5, 0.0),
+                           algo=os.environ.get("MLP_ALGO", "twoshot"))
         B = 512
         x = torch.randn(B, 784, device=dev).to(torch.bfloat16); y = torch.randint(0, 10, (B,), device=dev)
         def full():

@@ -47,7 +47,7 @@ def test_net_ddp_fused_peer(native_lib, tmp_path, use_graph):
     check_net_ddp(res, world, check_grads=not use_graph)
 
 
-@pytest.mark.parametrize("algo", ["oneshot", "twoshot"])
+@pytest.mark.parametrize("algo", ["oneshot", "twoshot", "nvls"])
 def test_mlp_ddp_peer(native_lib, tmp_path, algo):
     """bf16 MLP: replicas stay bit-identical; result tracks an fp32 single-process oracle."""
     from csed_514_project_distributed_training_using_pytorch_b200.models.mlp import WideMLP
