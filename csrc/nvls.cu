@@ -155,7 +155,9 @@ __global__ void __launch_bounds__(512) nvls_allreduce_kernel(CommDev c, NvlsArgs
         const size_t e0 = gv * N - a.state_base;      // multiple of N: 16-byte aligned state
         float4* mw = reinterpret_cast<float4*>(a.master + e0);
         float4* mb = reinterpret_cast<float4*>(a.mom + e0);
-        for (int q = 0; q < N / 4; ++q) {
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+          if (q >= N / 4) break;
           float4 w = mw[q], m = mb[q];
           float* wp = reinterpret_cast<float*>(&w);
           float* bp = reinterpret_cast<float*>(&m);
