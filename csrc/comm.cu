@@ -305,6 +305,18 @@ net_reduce_allreduce_sgd_ll_kernel(CommDev c, const float* __restrict__ partial,
   pdl_wait();      // partial rows come from kernel A; seq_ctr from the previous kernel B
   const unsigned seq = *seq_ctr + 1u;
   const unsigned slot = seq & 1u;
+  // this rank's batch loss: one warp of block 0, fixed summation order, off the tail
+  if (blockIdx.x == 0 && rg == 7) {
+    float l = 0.0f;
+    for (int r = cidx; r < G; r += 32) l += loss_partial[r];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) l += __shfl_down_sync(0xffffffffu, l, o);
+    if (cidx == 0 && loss_ring) {
+      const unsigned long long step = ctl[0];   // bumped only by the last CTA, after we arrive
+      loss_ring[step % (unsigned long long)ring] = l;
+      loss_ring[ring] = l;
+    }
+  }
   const float4 s = sum_partial_rows_256(partial, G, FLAT_SZ, col, valid, sm);
   __syncthreads();
   if (rg == 0) sm[0][cidx] = s;
@@ -316,6 +328,15 @@ net_reduce_allreduce_sgd_ll_kernel(CommDev c, const float* __restrict__ partial,
                  (((size_t)slot * c.world + c.rank) * N4 + col) * 2;
     st_volatile_u4(dst, make_uint4(__float_as_uint(mine.x), seq, __float_as_uint(mine.y), seq));
     st_volatile_u4(dst + 1, make_uint4(__float_as_uint(mine.z), seq, __float_as_uint(mine.w), seq));
+  }
+  // the update's own operands do not depend on the peers: fetch them while the tags fly
+  float4 pv = make_float4(0.f, 0.f, 0.f, 0.f), bv = pv;
+  float lr = 0.f, mu = 0.f;
+  if (rg == 0 && valid && params) {
+    pv = reinterpret_cast<float4*>(params)[col];
+    bv = reinterpret_cast<float4*>(mom)[col];
+    lr = hp[0];
+    mu = hp[1];
   }
   if (rg < c.world && valid) {
     float4 v = mine;
@@ -352,9 +373,6 @@ net_reduce_allreduce_sgd_ll_kernel(CommDev c, const float* __restrict__ partial,
     g.x *= inv; g.y *= inv; g.z *= inv; g.w *= inv;
     if (grad_out) reinterpret_cast<float4*>(grad_out)[col] = g;
     if (params) {
-      const float lr = hp[0], mu = hp[1];
-      float4 pv = reinterpret_cast<float4*>(params)[col];
-      float4 bv = reinterpret_cast<float4*>(mom)[col];
       bv.x = mu * bv.x + g.x; bv.y = mu * bv.y + g.y; bv.z = mu * bv.z + g.z; bv.w = mu * bv.w + g.w;
       pv.x -= lr * bv.x; pv.y -= lr * bv.y; pv.z -= lr * bv.z; pv.w -= lr * bv.w;
       reinterpret_cast<float4*>(params)[col] = pv;
@@ -366,14 +384,7 @@ net_reduce_allreduce_sgd_ll_kernel(CommDev c, const float* __restrict__ partial,
     if (prev == gridDim.x - 1) {
       *arrive_ctr = 0u;
       *seq_ctr = seq;
-      float l = 0.0f;
-      for (int r = 0; r < G; ++r) l += loss_partial[r];
-      const unsigned long long step = ctl[0];
-      if (loss_ring) {
-        loss_ring[step % (unsigned long long)ring] = l;
-        loss_ring[ring] = l;
-      }
-      ctl[0] = step + 1ull;
+      ctl[0] = ctl[0] + 1ull;
     }
   }
 }

@@ -674,15 +674,20 @@ net_reduce_sgd_kernel(const float* __restrict__ partial, int G, float* __restric
       reinterpret_cast<float4*>(mom)[i] = bv;
     }
   }
-  if (blockIdx.x == 0 && threadIdx.x == 64) {
+  if (blockIdx.x == 0 && (threadIdx.x >> 5) == 7) {   // one spare warp: loss + step counter
+    const int lane = threadIdx.x & 31;
     float l = 0.0f;
-    for (int r = 0; r < G; ++r) l += loss_partial[r];
-    const unsigned long long step = step_ptr ? *step_ptr : 0ull;
-    if (loss_ring) {  // slot [ring] always holds the latest step's loss
-      loss_ring[step % (unsigned long long)ring] = l;
-      loss_ring[ring] = l;
+    for (int r = lane; r < G; r += 32) l += loss_partial[r];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) l += __shfl_down_sync(0xffffffffu, l, o);
+    if (lane == 0) {
+      const unsigned long long step = step_ptr ? *step_ptr : 0ull;
+      if (loss_ring) {  // slot [ring] always holds the latest step's loss
+        loss_ring[step % (unsigned long long)ring] = l;
+        loss_ring[ring] = l;
+      }
+      if (step_ptr) *step_ptr = step + 1ull;
     }
-    if (step_ptr) *step_ptr = step + 1ull;
   }
 }
 
