@@ -156,7 +156,6 @@ def run_ours(a):
     run_steps(W)
     sync_all()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    launches0 = eng.launches
     e0.record()
     run_steps(K)
     e1.record()

@@ -53,7 +53,6 @@ _SIGS = {
     "b200_net_eval": [c_p, c_p, c_i, c_p, c_p, c_i, c_p, c_p, c_p, c_p, c_i, c_p],
 }
 _RESTYPES = {"b200_last_error": C.c_char_p}
-_OPTIONAL: dict[str, list] = {}  # filled by later modules via register_sigs()
 
 
 class NativeError(RuntimeError):
@@ -133,13 +132,3 @@ def ptr(t) -> int | None:
 
 def stream() -> int:
     return torch.cuda.current_stream().cuda_stream
-
-
-def require_cuda_contig(*tensors) -> None:
-    for t in tensors:
-        if t is None:
-            continue
-        if not t.is_cuda:
-            raise NativeError("expected a CUDA tensor")
-        if not t.is_contiguous():
-            raise NativeError("expected a contiguous tensor")

@@ -11,7 +11,7 @@ the bucket's fused all-reduce + SGD kernel overlaps the backward of the layers b
 """
 from __future__ import annotations
 
-from typing import Optional, Sequence
+from typing import Sequence
 
 import torch
 import torch.nn as nn

@@ -18,7 +18,6 @@ step lands in a device ring buffer and is read back per log interval, not per st
 from __future__ import annotations
 
 import ctypes
-from typing import Optional
 
 import torch
 

@@ -17,7 +17,6 @@ Two implementations behind one interface:
 from __future__ import annotations
 
 import ctypes as C
-import datetime
 import os
 from typing import Dict, Optional
 

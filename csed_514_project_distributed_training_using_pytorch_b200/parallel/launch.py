@@ -10,7 +10,6 @@ from __future__ import annotations
 
 import os
 import socket
-import sys
 import traceback
 from typing import Callable, Sequence
 

@@ -19,16 +19,14 @@ sampler, logging and checkpoints; multi-process through gloo.
 """
 from __future__ import annotations
 
-import math
 import os
-import time
 from typing import Optional
 
 import torch
 
 from .models import Net
 from .ops import net_ops
-from .ops.fused import FusedNetEngine, X_F32, X_F32_GATHER, X_U8, X_U8_GATHER
+from .ops.fused import FusedNetEngine, X_F32, X_U8, X_U8_GATHER
 from .ops.sgd import FlatSGD
 from .utils import checkpoint as ckpt
 from .utils.config import TrainConfig

@@ -6,7 +6,6 @@ import shutil
 import statistics
 import subprocess
 import threading
-import time
 from typing import Optional
 
 _Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"

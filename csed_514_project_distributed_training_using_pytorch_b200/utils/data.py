@@ -12,7 +12,7 @@ import gzip
 import os
 import struct
 from dataclasses import dataclass
-from typing import Optional, Tuple
+from typing import Optional
 
 import numpy as np
 import torch

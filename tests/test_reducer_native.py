@@ -1,0 +1,44 @@
+"""The native (C++) bucket planner and reducer core, on CPU (csrc/reducer.cpp)."""
+import pytest
+import torch
+
+from csed_514_project_distributed_training_using_pytorch_b200.parallel.reducer import (
+    ReducerCore, plan_buckets, plan_buckets_by_group)
+
+
+def test_planner_matches_torch_ddp_rule(native_lib):
+    # Net: all eight tensors in one bucket (`[[0..7]]`, 87,360 B)
+    net = [250 * 4, 10 * 4, 5000 * 4, 20 * 4, 16000 * 4, 50 * 4, 500 * 4, 10 * 4]
+    assert plan_buckets(net) == [0] * 8
+    # wide MLP in bf16: after the rebuild torch uses two buckets,
+    # [fc3.b, fc3.w, fc2.b, fc2.w] then [fc1.b, fc1.w]
+    mlp = [784 * 4096 * 2, 4096 * 2, 4096 * 4096 * 2, 4096 * 2, 4096 * 10 * 2, 10 * 2]
+    assert plan_buckets(mlp) == [1, 1, 0, 0, 0, 0]
+    # same rule as torch's own planner on an arbitrary list
+    sizes = [3 << 20, 100, 30 << 20, 2 << 20, 512, 700 << 10, 400 << 10]
+    params = [torch.empty(s // 4) for s in sizes]
+    import torch.distributed as dist
+    ref, _ = dist._compute_bucket_assignment_by_size(list(reversed(params)), [1 << 20, 25 << 20])
+    want = [0] * len(sizes)
+    for b, idxs in enumerate(ref):
+        for i in idxs:
+            want[len(sizes) - 1 - i] = b
+    assert plan_buckets(sizes) == want
+    assert plan_buckets_by_group(6, [0, 2, 4]) == [2, 2, 1, 1, 0, 0]
+    with pytest.raises(Exception):
+        plan_buckets_by_group(6, [1, 2])
+
+
+def test_reducer_core_ready_counting(native_lib):
+    core = ReducerCore([1, 1, 0, 0, 0, 0])
+    core.reset()
+    assert [core.mark_ready(i) for i in (5, 4, 3)] == [-1, -1, -1]
+    assert core.pending_buckets() == [0, 1]
+    assert core.mark_ready(2) == 0                 # bucket 0 complete
+    assert core.mark_ready(2) == -2                # marked twice -> caller raises
+    assert core.mark_ready(99) == -3
+    assert not core.all_done()
+    assert core.mark_ready(1) == -1 and core.mark_ready(0) == 1
+    assert core.all_done() and core.completion_order() == [0, 1]
+    core.reset()
+    assert core.pending_buckets() == [0, 1] and core.completion_order() == []
