@@ -551,6 +551,9 @@ net_fwdbwd_kernel(const float* __restrict__ params, const void* __restrict__ x, 
   for (int img = slot; img < B; img += nslots, ++it) {
     const bool first = (it == 0);
     load_image(f.xs, x, x_mode, img, gidx);
+    // the label is needed only after fc2, but its (dependent) global loads start now
+    int tgt = 0;
+    if (t < 32) tgt = (int)labels[(x_mode >= 2) ? gidx[img] : img];
     if (t < C2) {
       float m = 1.0f;
       if (mask_mode == 1) {
@@ -587,19 +590,17 @@ net_fwdbwd_kernel(const float* __restrict__ params, const void* __restrict__ x, 
     B200_PHASE(4);
     fc2_fwd_img(f.h1s, f.w4s, f.b4s, f.logit_s);
     __syncthreads();
-    if (t == 0) {
-      // fused log_softmax + NLL + its gradient (src/model.py:22 + src/train.py:74)
-      float lp[NCLS];
-      log_softmax10(f.logit_s, lp);
-      const int row_lab = (x_mode >= 2) ? gidx[img] : img;
-      const int tgt = (int)labels[row_lab];
-      float lt = 0.0f;
-#pragma unroll
-      for (int c = 0; c < NCLS; ++c) {
-        if (c == tgt) lt = lp[c];
-        f.dlog_s[c] = (expf(lp[c]) - (c == tgt ? 1.0f : 0.0f)) * inv_B;
-      }
-      loss_acc -= lt * inv_B;
+    if (t < 32) {
+      // fused log_softmax + NLL + its gradient (src/model.py:22 + src/train.py:74), one class
+      // per lane: max and sum by warp shuffles instead of a 20-long serial exp/log chain
+      const float z = (t < NCLS) ? f.logit_s[t] : -INFINITY;
+      const float mx = warp_max(z);
+      const float e = (t < NCLS) ? expf(z - mx) : 0.0f;
+      const float lse = mx + logf(warp_sum(e));
+      const float lp = z - lse;
+      if (t < NCLS) f.dlog_s[t] = (expf(lp) - (t == tgt ? 1.0f : 0.0f)) * inv_B;
+      const float lt = __shfl_sync(0xffffffffu, lp, tgt);
+      loss_acc -= lt * inv_B;       // every lane of warp 0 tracks it; lane 0 publishes
     }
     __syncthreads();
     B200_PHASE(5);
