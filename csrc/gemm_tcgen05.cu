@@ -30,6 +30,8 @@
 
 #include "comm.cuh"
 
+extern "C" int b200_pdl_enabled(void);
+
 namespace {
 
 constexpr int BM = 128;
@@ -235,10 +237,14 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, C::TMEM_COLS);
+  pdl_trigger();          // the next kernel in the stream may start its own prologue
   tcgen05_fence_before();
   __syncthreads();
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // Everything above (barrier init, TMEM allocation, descriptor prefetch) overlapped the tail
+  // of the previous kernel; operands and epilogue inputs may only be read from here on.
+  pdl_wait();
 
   if (warp == 0) {
     // ===== TMA producer =====
@@ -475,8 +481,8 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p, cu
     attr_done[dev & 63] = true;
   }
   dim3 grid((p.N + BN - 1) / BN, (p.M + BM - 1) / BM);
-  kern<<<grid, GEMM_THREADS, C::SMEM, s>>>(ma, mb, p);
-  B200_LAUNCH_OK();
+  B200_CUDA_OK(b200_launch_pdl(kern, grid, dim3(GEMM_THREADS), (size_t)C::SMEM, s,
+                               b200_pdl_enabled() != 0, ma, mb, p));
   return 0;
 }
 
