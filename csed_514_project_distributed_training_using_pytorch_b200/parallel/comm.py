@@ -65,6 +65,24 @@ class CommError(RuntimeError):
     pass
 
 
+_CROSSOVER = None
+
+
+def _crossover_table() -> dict:
+    """profiles/allreduce_crossover.json (written by scripts/sweep_report.py from the measured
+    sweep): per world size, the largest payload for which the one-shot kernel won."""
+    global _CROSSOVER
+    if _CROSSOVER is None:
+        import json
+        from pathlib import Path
+        p = Path(__file__).resolve().parents[2] / "profiles" / "allreduce_crossover.json"
+        try:
+            _CROSSOVER = json.loads(p.read_text())
+        except Exception:
+            _CROSSOVER = {}
+    return _CROSSOVER
+
+
 class _RawCudaMemory:
     """Exposes a raw device allocation to torch through __cuda_array_interface__."""
 
@@ -467,6 +485,10 @@ class PeerComm(BaseComm):
         """Measured crossover (profiles/allreduce_sweep.md): the tagged one-shot wins while the
         bytes every rank must absorb, (world-1) x payload, stay small (<= 1 MiB at 2 GPUs,
         <= 32 KiB at 8); the two-shot wins above."""
+        if "B200DP_ONESHOT_MAX_KB" not in os.environ:
+            tab = _crossover_table().get(str(self.world_size))
+            if tab is not None:          # measured on this kind of box for this world size
+                return 0 if nbytes <= tab["oneshot_max_bytes"] else 1
         budget = int(os.environ.get("B200DP_ONESHOT_MAX_KB", "256")) << 10
         return 0 if nbytes * max(1, self.world_size - 1) <= budget else 1
 

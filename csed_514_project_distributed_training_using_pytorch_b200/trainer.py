@@ -11,8 +11,10 @@ Execution on a GPU (default): the dataset is uploaded to HBM once as uint8 (47 M
 epoch's sample order is uploaded once per epoch (240 KB), and every optimizer step is ONE
 CUDA-graph replay of two kernels (ops/fused.py); the kernel gathers + normalises its own
 batch from the step counter, so the hot loop has no host->device traffic and no host sync.
-Losses are read back from a device ring once per log interval (K18). `stream=True` keeps
-the dataset in pinned host memory instead and copies each batch up per step.
+Losses are read back from a device ring once per log interval (K18). `feed="host"` keeps
+the dataset in pinned host memory instead: the epoch's shuffled order is gathered on the host
+into a pinned buffer and the native runner copies one batch up per step (the role of the
+reference's DataLoader(pin_memory=True), src/train_dist.py:40-45).
 
 Execution on CPU (`device="cpu"`, BASELINE config 1): the PyTorch oracle path with the same
 sampler, logging and checkpoints; multi-process through gloo.
@@ -148,8 +150,50 @@ class Trainer:
         sampler = self._sampler()
         sampler.set_epoch(epoch if self.distributed_style else epoch - 1)
         if self.device.type == "cuda" and self.engine is not None:
+            if self.cfg.feed == "host":
+                return self._train_epoch_host_feed(epoch, sampler)
             return self._train_epoch_fused(epoch, sampler)
         return self._train_epoch_autograd(epoch, sampler)
+
+    def _train_epoch_host_feed(self, epoch: int, sampler: ShardSampler) -> float:
+        """Dataset stays on the host: gather this epoch's order into pinned memory once, then
+        stream it through the native runner (H2D per step, copy/compute overlap)."""
+        c = self.cfg
+        B = c.rank_batch() if self.distributed_style else c.batch_size_train
+        idx = sampler.indices()
+        n = idx.numel()
+        if getattr(self, "_host_x", None) is None or self._host_x.shape[0] != n:
+            self._host_x = torch.empty(n, 784, dtype=torch.uint8).pin_memory()
+            self._host_y = torch.empty(n, dtype=torch.int64).pin_memory()
+        torch.index_select(self.train_set.images, 0, idx, out=self._host_x)
+        torch.index_select(self.train_set.labels, 0, idx, out=self._host_y)
+        full, tail = n // B, n % B
+        n_dataset = len(self.train_set)
+        batches = sampler.batches(B)
+        losses = []
+        if full:
+            losses.append(self.train_steps_from_host(self._host_x, self._host_y, full, B))
+        if tail:
+            losses.append(self.train_steps_from_host(self._host_x[full * B:], self._host_y[full * B:],
+                                                     1, tail))
+        torch.cuda.synchronize(self.device)
+        if self.comm is not None:
+            self.comm.check_errors()
+        epoch_loss = 0.0
+        flat = torch.cat(losses).tolist() if losses else []
+        for bi, l in enumerate(flat):
+            blen = batches[bi][1]
+            epoch_loss += l / blen
+            if self.distributed_style:
+                self.log.train_losses.append(l)
+                self.log.train_counter.append(bi * 64 + epoch * n_dataset)
+            elif bi % c.log_interval == 0:
+                self.log.train_log(epoch, bi, blen, n_dataset, len(batches), l,
+                                   bi * 64 + (epoch - 1) * n_dataset)
+        if not self.distributed_style and c.checkpoint_every_log:
+            self.save()
+        self.examples_seen += n
+        return epoch_loss
 
     UNROLL = 16   # steps per captured graph in the resident path (PDL spans step boundaries)
 

@@ -41,6 +41,8 @@ class TrainConfig:
     cuda_graph: bool = True
     dropout: bool = True
     input_dtype: str = "u8"         # how the dataset is stored: "u8" (MNIST native) or "f32"
+    feed: str = "resident"          # "resident": dataset in HBM, the kernel gathers its batch;
+                                    # "host": dataset in pinned host memory, one H2D copy per step
 
     def rank_batch(self) -> int:
         if self.per_rank_batch > 0:

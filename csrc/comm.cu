@@ -787,8 +787,10 @@ int b200_comm_allreduce(const void* comm, int dtype, int algo, int update, const
   B200_REQUIRE(need <= a.src_vec, "b200_comm_allreduce: %zu B per source exceed the staging (%zu B)",
                need * 16, src_bytes);
   if (blocks <= 0) {
+    // one-shot is latency bound: spread it wide (one 16-byte vector per thread, up to 64 CTAs);
+    // two-shot moves bulk data: ~32 KB per CTA
     const size_t work = (algo == 0) ? a.nvec : (a.nvec + c.world - 1) / c.world;
-    blocks = (int)((work + 2047) / 2048);  // ~32 KB per CTA
+    blocks = (algo == 0) ? (int)((work + AR_THREADS - 1) / AR_THREADS) : (int)((work + 2047) / 2048);
     const int cap = (algo == 0) ? 64 : gmax;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;

@@ -26,5 +26,19 @@ for n, f in ((8, "allreduce_sweep_n8_raw.json"), (2, "allreduce_sweep_n2_raw.jso
         out.append(f"| {r['bytes']} | {g('oneshot_us')} | {g('twoshot_us')} | {g('nvls_us')} | {g('nccl_us')} | "
                    f"{r['nccl_us'] / ours[best]:.2f}x ({best[:-3]}) | {bus:.1f} | {bus / LINK:.2f} |")
     out.append("")
+# crossover table consumed by PeerComm.choose_algo: per world size, the largest payload (bytes)
+# for which the tagged one-shot kernel measured faster than the two-shot kernel
+table = {}
+for n, f in ((8, "allreduce_sweep_n8_raw.json"), (2, "allreduce_sweep_n2_raw.json")):
+    p = ROOT / "profiles" / f
+    if not p.exists():
+        continue
+    txt = p.read_text(); d = json.loads(txt[txt.find("{\n"):txt.rfind("}") + 1])
+    best = 0
+    for r in d["sweep"]:
+        if "oneshot_us" in r and "twoshot_us" in r and r["oneshot_us"] <= r["twoshot_us"]:
+            best = max(best, r["bytes"])
+    table[str(n)] = {"oneshot_max_bytes": best}
+(ROOT / "profiles" / "allreduce_crossover.json").write_text(json.dumps(table, indent=1) + "\n")
 (ROOT / "profiles" / "allreduce_sweep.md").write_text("\n".join(out) + "\n")
 print("\n".join(out))

@@ -288,3 +288,31 @@ def test_net_with_tcgen05_conv2_trains(cuda_device):
     for p_, q in zip(net.param_list(), op):
         err = (p_.grad.cpu() - q.grad.float()).norm() / (q.grad.float().norm() + 1e-12)
         assert err < 2e-2
+
+
+def test_resident_epoch_multistep_graph_equals_eager(cuda_device):
+    """Device-side index stepping + 16-step graphs (PDL across steps) == one eager step at a time."""
+    from csed_514_project_distributed_training_using_pytorch_b200.ops.fused import X_U8_GATHER
+    g = torch.Generator().manual_seed(0)
+    n, B = 64 * 40, 64
+    data = torch.randint(0, 256, (n, 784), dtype=torch.uint8, generator=g).to(cuda_device)
+    labels = torch.randint(0, 10, (n,), generator=g).to(cuda_device)
+    perm = torch.randperm(n, generator=g).to(torch.int32).to(cuda_device)
+    out = []
+    for mode in ("eager", "graph16"):
+        eng = FusedNetEngine(_net(cuda_device).train(), lr=0.02, momentum=0.5, seed=5)
+        eng.begin_epoch()
+        if mode == "eager":
+            for _ in range(40):
+                eng.step(data, labels, X_U8_GATHER, gidx=perm, batch=B, idx_stride=B)
+        else:
+            g16 = eng.capture(data, labels, X_U8_GATHER, gidx=perm, batch=B, idx_stride=B, unroll=16)
+            g1 = eng.capture(data, labels, X_U8_GATHER, gidx=perm, batch=B, idx_stride=B)
+            g16.replay(); g16.replay()
+            for _ in range(8):
+                g1.replay()
+        torch.cuda.synchronize()
+        assert eng.steps_done() == 40
+        out.append((eng.flat.param.clone(), eng.last_losses(40).clone()))
+    assert torch.equal(out[0][0], out[1][0])
+    assert torch.equal(out[0][1], out[1][1])

@@ -68,3 +68,21 @@ def test_trainer_layered_path_matches_fused_first_steps(cuda_device):
         torch.cuda.synchronize()
         res.append(tr.flat.param.clone())
     torch.testing.assert_close(res[0], res[1], rtol=2e-3, atol=2e-4)
+
+
+def test_trainer_host_feed_matches_resident(cuda_device):
+    """feed="host" (pinned dataset, native runner, H2D per step) follows exactly the same
+    trajectory as the device-resident feed: same kernels, same batches, same dropout keys."""
+    data = synthetic_mnist(64 * 20 + 9, seed=5)
+    res = []
+    for feed in ("resident", "host"):
+        cfg = TrainConfig(epochs=1, train_size=len(data), test_size=100, feed=feed,
+                          checkpoint_every_log=False, learning_rate=0.02)
+        tr = Trainer(cfg, distributed_style=False)
+        tr.set_data(data, synthetic_mnist(100, seed=6))
+        tr.log.quiet = True
+        tr.train_epoch(1)
+        torch.cuda.synchronize()
+        res.append((tr.flat.param.clone(), list(tr.log.train_losses)))
+    assert torch.equal(res[0][0], res[1][0])
+    assert res[0][1] == res[1][1]
