@@ -53,16 +53,21 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
                "r"(bytes)
                : "memory");
 }
+// Bounded: a protocol bug traps (CUDA error) after ~2 s instead of hanging the GPU.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "WAIT_%=:\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-      "@p bra DONE_%=;\n\t"
-      "bra WAIT_%=;\n\t"
-      "DONE_%=:\n\t}" ::"r"(smem_u32(bar)),
-      "r"(parity)
-      : "memory");
+  const long long t0 = clock64();
+  for (;;) {
+    uint32_t done;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    if (done) return;
+    if (clock64() - t0 > 4000000000ll) __trap();
+  }
 }
 __device__ __forceinline__ void fence_barrier_init() {
   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -197,6 +202,132 @@ template <int BN, bool B_MN> struct Cfg {
   static constexpr int TMEM_COLS = BN < 32 ? 32 : BN;
 };
 
+// ===== epilogue (shared by the 1-CTA and the 2-CTA kernels): warps 2..5 =====
+template <int BN>
+__device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint8_t* tiles,
+                                              uint64_t* tmem_full, uint32_t tmem_base, int warp,
+                                              int lane, int m0, int n0) {
+  // Accumulator rows arrive one per lane (tcgen05.ld 32x32b). Bias / ReLU / mask are applied
+  // in registers. bf16 results are then staged through shared memory (the tile ring is free
+  // once tmem_full has fired) so each warp writes whole 16-byte-vector rows: a store
+  // instruction covers 512 contiguous bytes instead of 32 scattered 16-byte pieces. That
+  // matters most for the reduce-scatter epilogue, whose stores cross NVLink.
+  const int lg = warp & 3;
+  mbar_wait(tmem_full, 0);
+  tcgen05_fence_after();
+  const int row = m0 + lg * 32 + lane;
+  const bool row_ok = row < p.M;
+  constexpr int CHUNK = BN >= 32 ? 32 : 16;
+  constexpr int PITCH = BN * 2 + 16;                       // bytes per staged row
+  uint8_t* sbuf = tiles + lg * (32 * PITCH);
+#pragma unroll 1
+  for (int c0 = 0; c0 < BN; c0 += CHUNK) {
+    uint32_t r[CHUNK];
+    const uint32_t taddr = tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)c0;
+    if constexpr (CHUNK == 32) tmem_ld32(taddr, r); else tmem_ld16(taddr, r);
+    tmem_ld_wait();
+    const int col0 = n0 + c0;
+    float v[CHUNK];
+#pragma unroll
+    for (int j = 0; j < CHUNK; ++j) v[j] = __uint_as_float(r[j]);
+    if (p.bias) {
+#pragma unroll
+      for (int j = 0; j < CHUNK; ++j)
+        if (col0 + j < p.N) v[j] += __bfloat162float(p.bias[col0 + j]);
+    }
+    if (p.relu) {
+#pragma unroll
+      for (int j = 0; j < CHUNK; ++j) v[j] = fmaxf(v[j], 0.0f);
+    }
+    if (p.relu_mask && row_ok) {
+      const __nv_bfloat16* mrow = p.relu_mask + (size_t)row * p.ld_mask + col0;
+      if (col0 + CHUNK <= p.N && (p.ld_mask % 8) == 0) {
+#pragma unroll
+        for (int j = 0; j < CHUNK; j += 8) {
+          const uint4 mv = *reinterpret_cast<const uint4*>(mrow + j);
+          const uint32_t w[4] = {mv.x, mv.y, mv.z, mv.w};
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            if (__uint_as_float(w[q] << 16) <= 0.0f) v[j + 2 * q] = 0.0f;
+            if (__uint_as_float(w[q] & 0xffff0000u) <= 0.0f) v[j + 2 * q + 1] = 0.0f;
+          }
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < CHUNK; ++j)
+          if (col0 + j < p.N && __bfloat162float(mrow[j]) <= 0.0f) v[j] = 0.0f;
+      }
+    }
+    if (p.c_fp32) {
+      if (row_ok) {
+        float* crow = reinterpret_cast<float*>(p.C) + (size_t)row * p.ldc + col0;
+        if (col0 + CHUNK <= p.N && (p.ldc % 4) == 0) {
+#pragma unroll
+          for (int j = 0; j < CHUNK; j += 4)
+            *reinterpret_cast<float4*>(crow + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+        } else {
+#pragma unroll
+          for (int j = 0; j < CHUNK; ++j)
+            if (col0 + j < p.N) crow[j] = v[j];
+        }
+      }
+    } else {
+      // pack to bf16 and park this lane's row segment in shared memory
+#pragma unroll
+      for (int j = 0; j < CHUNK; j += 8) {
+        uint32_t w[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const __nv_bfloat162 h = __floats2bfloat162_rn(v[j + 2 * q], v[j + 2 * q + 1]);
+          w[q] = *reinterpret_cast<const uint32_t*>(&h);
+        }
+        *reinterpret_cast<uint4*>(sbuf + lane * PITCH + (c0 + j) * 2) = make_uint4(w[0], w[1], w[2], w[3]);
+      }
+    }
+  }
+  if (!p.c_fp32) {
+    __syncwarp();
+    constexpr int VPR = BN / 8;                   // 16-byte vectors per tile row
+    constexpr int RPI = 32 / VPR;                 // rows written per warp-wide store
+    const int cv = lane % VPR;
+    const int col = n0 + cv * 8;
+    const bool vec_ok = (p.ldc % 8) == 0 && ((reinterpret_cast<uintptr_t>(p.C) & 15) == 0);
+    unsigned slot = 0;
+    size_t slot_vec = 0;
+    if (p.rs_on) {
+      slot = (*p.rs_seq + 1u) & 1u;
+      slot_vec = (size_t)p.rs_comm.world * p.rs_src_vec;
+    }
+#pragma unroll 1
+    for (int it = 0; it < VPR; ++it) {           // 32 rows / RPI rows per iteration == VPR
+      const int rl = it * RPI + lane / VPR;
+      const int grow = m0 + lg * 32 + rl;
+      if (grow >= p.M || col >= p.N) continue;
+      const uint4 val = *reinterpret_cast<const uint4*>(sbuf + rl * PITCH + cv * 16);
+      if (p.rs_on) {
+        // reduce-scatter epilogue: vector `vec` of the bucket goes to owner vec / sl
+        if (col + 8 <= p.N) {
+          const size_t vec = p.rs_base_vec + ((size_t)grow * p.ldc + col) / 8;
+          const int owner = (int)(vec / p.rs_sl);
+          uint4* dst = peer_ptr<uint4>(p.rs_comm, owner, p.rs_stage_off) + slot * slot_vec +
+                       (size_t)p.rs_comm.rank * p.rs_src_vec + (vec - (size_t)owner * p.rs_sl);
+          *dst = val;
+        }
+      } else {
+        __nv_bfloat16* cptr = reinterpret_cast<__nv_bfloat16*>(p.C) + (size_t)grow * p.ldc + col;
+        if (vec_ok && col + 8 <= p.N) {
+          *reinterpret_cast<uint4*>(cptr) = val;
+        } else {
+          const __nv_bfloat16* sv = reinterpret_cast<const __nv_bfloat16*>(&val);
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            if (col + j < p.N) cptr[j] = sv[j];
+        }
+      }
+    }
+  }
+}
+
 template <int BN, bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
@@ -298,132 +429,191 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
       umma_commit(tmem_full);            // accumulator complete
     }
   } else {
-    // ===== epilogue: warps 2..5, TMEM lane group = warp % 4 =====
-    // Accumulator rows arrive one per lane (tcgen05.ld 32x32b). Bias / ReLU / mask are applied
-    // in registers. bf16 results are then staged through shared memory (the tile ring is free
-    // once tmem_full has fired) so each warp writes whole 16-byte-vector rows: a store
-    // instruction covers 512 contiguous bytes instead of 32 scattered 16-byte pieces. That
-    // matters most for the reduce-scatter epilogue, whose stores cross NVLink.
-    const int lg = warp & 3;
-    mbar_wait(tmem_full, 0);
-    tcgen05_fence_after();
-    const int row = m0 + lg * 32 + lane;
-    const bool row_ok = row < p.M;
-    constexpr int CHUNK = BN >= 32 ? 32 : 16;
-    constexpr int PITCH = BN * 2 + 16;                       // bytes per staged row
-    uint8_t* sbuf = tiles + lg * (32 * PITCH);
-#pragma unroll 1
-    for (int c0 = 0; c0 < BN; c0 += CHUNK) {
-      uint32_t r[CHUNK];
-      const uint32_t taddr = tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)c0;
-      if constexpr (CHUNK == 32) tmem_ld32(taddr, r); else tmem_ld16(taddr, r);
-      tmem_ld_wait();
-      const int col0 = n0 + c0;
-      float v[CHUNK];
-#pragma unroll
-      for (int j = 0; j < CHUNK; ++j) v[j] = __uint_as_float(r[j]);
-      if (p.bias) {
-#pragma unroll
-        for (int j = 0; j < CHUNK; ++j)
-          if (col0 + j < p.N) v[j] += __bfloat162float(p.bias[col0 + j]);
-      }
-      if (p.relu) {
-#pragma unroll
-        for (int j = 0; j < CHUNK; ++j) v[j] = fmaxf(v[j], 0.0f);
-      }
-      if (p.relu_mask && row_ok) {
-        const __nv_bfloat16* mrow = p.relu_mask + (size_t)row * p.ld_mask + col0;
-        if (col0 + CHUNK <= p.N && (p.ld_mask % 8) == 0) {
-#pragma unroll
-          for (int j = 0; j < CHUNK; j += 8) {
-            const uint4 mv = *reinterpret_cast<const uint4*>(mrow + j);
-            const uint32_t w[4] = {mv.x, mv.y, mv.z, mv.w};
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-              if (__uint_as_float(w[q] << 16) <= 0.0f) v[j + 2 * q] = 0.0f;
-              if (__uint_as_float(w[q] & 0xffff0000u) <= 0.0f) v[j + 2 * q + 1] = 0.0f;
-            }
-          }
-        } else {
-#pragma unroll
-          for (int j = 0; j < CHUNK; ++j)
-            if (col0 + j < p.N && __bfloat162float(mrow[j]) <= 0.0f) v[j] = 0.0f;
-        }
-      }
-      if (p.c_fp32) {
-        if (row_ok) {
-          float* crow = reinterpret_cast<float*>(p.C) + (size_t)row * p.ldc + col0;
-          if (col0 + CHUNK <= p.N && (p.ldc % 4) == 0) {
-#pragma unroll
-            for (int j = 0; j < CHUNK; j += 4)
-              *reinterpret_cast<float4*>(crow + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-          } else {
-#pragma unroll
-            for (int j = 0; j < CHUNK; ++j)
-              if (col0 + j < p.N) crow[j] = v[j];
-          }
-        }
-      } else {
-        // pack to bf16 and park this lane's row segment in shared memory
-#pragma unroll
-        for (int j = 0; j < CHUNK; j += 8) {
-          uint32_t w[4];
-#pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            const __nv_bfloat162 h = __floats2bfloat162_rn(v[j + 2 * q], v[j + 2 * q + 1]);
-            w[q] = *reinterpret_cast<const uint32_t*>(&h);
-          }
-          *reinterpret_cast<uint4*>(sbuf + lane * PITCH + (c0 + j) * 2) = make_uint4(w[0], w[1], w[2], w[3]);
-        }
-      }
-    }
-    if (!p.c_fp32) {
-      __syncwarp();
-      constexpr int VPR = BN / 8;                   // 16-byte vectors per tile row
-      constexpr int RPI = 32 / VPR;                 // rows written per warp-wide store
-      const int cv = lane % VPR;
-      const int col = n0 + cv * 8;
-      const bool vec_ok = (p.ldc % 8) == 0 && ((reinterpret_cast<uintptr_t>(p.C) & 15) == 0);
-      unsigned slot = 0;
-      size_t slot_vec = 0;
-      if (p.rs_on) {
-        slot = (*p.rs_seq + 1u) & 1u;
-        slot_vec = (size_t)p.rs_comm.world * p.rs_src_vec;
-      }
-#pragma unroll 1
-      for (int it = 0; it < VPR; ++it) {           // 32 rows / RPI rows per iteration == VPR
-        const int rl = it * RPI + lane / VPR;
-        const int grow = m0 + lg * 32 + rl;
-        if (grow >= p.M || col >= p.N) continue;
-        const uint4 val = *reinterpret_cast<const uint4*>(sbuf + rl * PITCH + cv * 16);
-        if (p.rs_on) {
-          // reduce-scatter epilogue: vector `vec` of the bucket goes to owner vec / sl
-          if (col + 8 <= p.N) {
-            const size_t vec = p.rs_base_vec + ((size_t)grow * p.ldc + col) / 8;
-            const int owner = (int)(vec / p.rs_sl);
-            uint4* dst = peer_ptr<uint4>(p.rs_comm, owner, p.rs_stage_off) + slot * slot_vec +
-                         (size_t)p.rs_comm.rank * p.rs_src_vec + (vec - (size_t)owner * p.rs_sl);
-            *dst = val;
-          }
-        } else {
-          __nv_bfloat16* cptr = reinterpret_cast<__nv_bfloat16*>(p.C) + (size_t)grow * p.ldc + col;
-          if (vec_ok && col + 8 <= p.N) {
-            *reinterpret_cast<uint4*>(cptr) = val;
-          } else {
-            const __nv_bfloat16* sv = reinterpret_cast<const __nv_bfloat16*>(&val);
-#pragma unroll
-            for (int j = 0; j < 8; ++j)
-              if (col + j < p.N) cptr[j] = sv[j];
-          }
-        }
-      }
-    }
+    epilogue_tile<BN>(p, tiles, tmem_full, tmem_base, warp, lane, m0, n0);
   }
   tcgen05_fence_before();
   __syncthreads();
   if (warp == 1) {
     tcgen05_fence_after();
     tmem_dealloc(tmem_base, C::TMEM_COLS);
+  }
+}
+
+// ===========================================================================
+// 2-CTA variant: a thread-block cluster of two CTAs (one TPC) computes a 256 x BN tile with
+// tcgen05.mma.cta_group::2. Each CTA stages ITS 128 rows of A and ITS half (BN/2 columns) of
+// B; the pair's tensor cores read both halves, so every byte of B is fetched from L2 once per
+// 256 output rows instead of once per 128: the L2 -> SM operand traffic that caps the 1-CTA
+// kernel at ~47 % tensor-pipe activity is cut by a quarter (BN=128) to a half (BN=256).
+//   * both CTAs issue their TMA loads with .cta_group::2 and complete them on the LEADER's
+//     `full` barrier (address obtained with mapa); the peer also arrives there remotely
+//   * only the leader's elected thread issues the MMAs; tcgen05.commit ... multicast::cluster
+//     releases the stage in both CTAs and finally raises tmem_full in both
+//   * each CTA drains its own 128 TMEM lanes with the common epilogue
+// ===========================================================================
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t mapa_shared(uint32_t local_addr, uint32_t cta_rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_addr), "r"(cta_rank));
+  return r;
+}
+__device__ __forceinline__ void mbar_expect_tx_cluster(uint32_t cluster_addr, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.release.cluster.shared::cluster.b64 _, [%0], %1;" ::"r"(
+                   cluster_addr),
+               "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_2sm(void* dst, const CUtensorMap* map,
+                                                uint32_t leader_bar_cluster_addr, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4}], [%2];" ::"r"(smem_u32(dst)),
+      "l"(map), "r"(leader_bar_cluster_addr), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_alloc_2sm(uint32_t* dst_smem, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                   smem_u32(dst_smem)),
+               "r"(ncols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc_2sm(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols)
+               : "memory");
+}
+__device__ __forceinline__ void umma_bf16_2sm(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,
+                                              uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit_2sm(uint64_t* bar) {   // same offset in both CTAs
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64"
+      " [%0], %1;" ::"r"(smem_u32(bar)),
+      "h"((uint16_t)3)
+      : "memory");
+}
+
+template <int BN, bool B_MN> struct Cfg2 {
+  static constexpr int A_BYTES = BM * BK * 2;              // this CTA's 128 rows
+  static constexpr int B_BYTES = (BN / 2) * BK * 2;        // this CTA's half of the columns
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int STAGES = (BN >= 256) ? 6 : 8;
+  static constexpr int SMEM = STAGES * STAGE_BYTES + 1024 + 256;
+  static constexpr int TMEM_COLS = BN;
+};
+
+template <int BN, bool A_MN, bool B_MN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
+gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap map_a,
+                              const __grid_constant__ CUtensorMap map_b, GemmParams p) {
+  using C = Cfg2<BN, B_MN>;
+  static_assert(BN == 128 || BN == 256, "2-CTA tiles are 256x128 or 256x256");
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~(uintptr_t)1023);
+  uint8_t* tiles = smem;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + C::STAGES * C::STAGE_BYTES);
+  uint64_t* empty = full + C::STAGES;
+  uint64_t* tmem_full = empty + C::STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();                 // 0 = leader
+  const int m0 = (blockIdx.x >> 1) * 256 + (int)rank * BM; // this CTA's rows
+  const int n0 = blockIdx.y * BN;
+  const int nb0 = n0 + (int)rank * (BN / 2);               // this CTA's half of B
+  const int num_kb = (p.K + BK - 1) / BK;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&map_a);
+    tma_prefetch_desc(&map_b);
+    for (int s = 0; s < C::STAGES; ++s) {
+      mbar_init(&full[s], 2);     // one arrive.expect_tx from each CTA's producer (leader's copy is used)
+      mbar_init(&empty[s], 1);    // one multicast commit from the leader's MMA thread
+    }
+    mbar_init(tmem_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc_2sm(tmem_slot, C::TMEM_COLS);
+  pdl_trigger();
+  tcgen05_fence_before();
+  cluster_sync_all();            // both CTAs' barriers and TMEM are ready before anyone signals
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();
+
+  if (warp == 0) {
+    // ===== TMA producer (both CTAs) =====
+    if (lane == 0) {
+      for (int kb = 0; kb < num_kb; ++kb) {
+        const int s = kb % C::STAGES;
+        const uint32_t ph = (kb / C::STAGES) & 1;
+        mbar_wait(&empty[s], ph ^ 1);
+        uint8_t* a_dst = tiles + s * C::STAGE_BYTES;
+        uint8_t* b_dst = a_dst + C::A_BYTES;
+        const uint32_t lead_full = mapa_shared(smem_u32(&full[s]), 0);
+        mbar_expect_tx_cluster(lead_full, C::STAGE_BYTES);
+        const int k0 = kb * BK;
+        if (A_MN) {
+          tma_load_2d_2sm(a_dst, &map_a, lead_full, m0, k0);
+          tma_load_2d_2sm(a_dst + BK * 128, &map_a, lead_full, m0 + 64, k0);
+        } else {
+          tma_load_2d_2sm(a_dst, &map_a, lead_full, k0, m0);
+        }
+        if (B_MN) {
+#pragma unroll
+          for (int j = 0; j < BN / 2 / 64; ++j)
+            tma_load_2d_2sm(b_dst + j * BK * 128, &map_b, lead_full, nb0 + 64 * j, k0);
+        } else {
+          tma_load_2d_2sm(b_dst, &map_b, lead_full, k0, nb0);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer (leader CTA only) =====
+    if (rank == 0 && lane == 0) {
+      constexpr uint32_t idesc = make_idesc(256, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
+      for (int kb = 0; kb < num_kb; ++kb) {
+        const int s = kb % C::STAGES;
+        const uint32_t ph = (kb / C::STAGES) & 1;
+        mbar_wait(&full[s], ph);
+        tcgen05_fence_after();
+        const uint32_t a_addr = smem_u32(tiles + s * C::STAGE_BYTES);
+        const uint32_t b_addr = a_addr + C::A_BYTES;
+#pragma unroll
+        for (int k = 0; k < BK / UMMA_K; ++k) {
+          const uint64_t adesc = A_MN ? make_smem_desc(a_addr + k * UMMA_K * 128, BK * 128, 1024)
+                                      : make_smem_desc(a_addr + k * UMMA_K * 2, 16, 1024);
+          const uint64_t bdesc = B_MN ? make_smem_desc(b_addr + k * UMMA_K * 128, BK * 128, 1024)
+                                      : make_smem_desc(b_addr + k * UMMA_K * 2, 16, 1024);
+          umma_bf16_2sm(tmem_base, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+        }
+        umma_commit_2sm(&empty[s]);      // frees the stage in BOTH CTAs
+      }
+      umma_commit_2sm(tmem_full);        // accumulators complete in both CTAs
+    }
+  } else {
+    epilogue_tile<BN>(p, tiles, tmem_full, tmem_base, warp, lane, m0, n0);
+  }
+  tcgen05_fence_before();
+  cluster_sync_all();            // nobody frees TMEM or exits while the peer still depends on it
+  if (warp == 1) {
+    tcgen05_fence_after();
+    tmem_dealloc_2sm(tmem_base, C::TMEM_COLS);
   }
 }
 
@@ -486,6 +676,48 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p, cu
   return 0;
 }
 
+template <int BN, bool A_MN, bool B_MN>
+int launch_2cta(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p, cudaStream_t s) {
+  using C = Cfg2<BN, B_MN>;
+  auto kern = gemm_bf16_tcgen05_2cta_kernel<BN, A_MN, B_MN>;
+  static bool attr_done[64] = {false};
+  int dev = 0;
+  B200_CUDA_OK(cudaGetDevice(&dev));
+  if (!attr_done[dev & 63]) {
+    B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM));
+    attr_done[dev & 63] = true;
+  }
+  dim3 grid(2 * ((p.M + 255) / 256), (p.N + BN - 1) / BN);   // cluster pairs along x
+  B200_CUDA_OK(b200_launch_pdl(kern, grid, dim3(GEMM_THREADS), (size_t)C::SMEM, s,
+                               b200_pdl_enabled() != 0, ma, mb, p));
+  return 0;
+}
+
+template <int BN>
+int dispatch_major_2cta(int a_mn, int b_mn, const CUtensorMap& ma, const CUtensorMap& mb,
+                        const GemmParams& p, cudaStream_t s) {
+  if (!a_mn && !b_mn) return launch_2cta<BN, false, false>(ma, mb, p, s);
+  if (!a_mn && b_mn) return launch_2cta<BN, false, true>(ma, mb, p, s);
+  if (a_mn && b_mn) return launch_2cta<BN, true, true>(ma, mb, p, s);
+  return launch_2cta<BN, true, false>(ma, mb, p, s);
+}
+
+// 2-CTA tiles are used when the problem is big enough to fill the machine with 256-row
+// pairs (B200DP_GEMM_2CTA=0 disables, =1 forces whenever the shape allows).
+int use_2cta(int M, int N, bool rs_on) {
+  static int mode = -1;
+  if (mode < 0) {
+    const char* e = getenv("B200DP_GEMM_2CTA");
+    mode = e ? (e[0] == '0' ? 0 : (e[0] == '1' ? 1 : 2)) : 2;
+  }
+  if (mode == 0 || rs_on || N < 128 || M <= 128) return 0;
+  const long long pairs256 = (long long)((M + 255) / 256) * ((N + 255) / 256);
+  if (N >= 256 && (mode == 1 || pairs256 * 2 >= 120)) return 256;
+  const long long pairs128 = (long long)((M + 255) / 256) * ((N + 127) / 128);
+  if (mode == 1 || pairs128 * 2 >= 100) return 128;
+  return 0;
+}
+
 template <int BN>
 int dispatch_major(int a_mn, int b_mn, const CUtensorMap& ma, const CUtensorMap& mb,
                    const GemmParams& p, cudaStream_t s) {
@@ -531,12 +763,15 @@ int b200_gemm_bf16_rs(const void* A, int a_mn, long long lda, const void* B, int
                       size_t rs_slice_vec, size_t rs_base_vec, const unsigned* rs_seq,
                       void* stream) {
   B200_REQUIRE(M > 0 && N > 0 && K > 0, "b200_gemm_bf16: empty problem");
-  const int BN = (N <= 16) ? 16 : (N <= 32 ? 32 : (N <= 64 ? 64 : 128));
+  const int bn2 = use_2cta(M, N, rs_comm != nullptr);
+  const int BN = bn2 ? bn2 : ((N <= 16) ? 16 : (N <= 32 ? 32 : (N <= 64 ? 64 : 128)));
   CUtensorMap ma, mb;
   int e;
   if (a_mn) e = make_map(&ma, A, K, M, lda, 64, 64); else e = make_map(&ma, A, M, K, lda, 64, BM);
   if (e) return e;
-  if (b_mn) e = make_map(&mb, B, K, N, ldb, 64, 64); else e = make_map(&mb, B, N, K, ldb, 64, BN);
+  // with 2-CTA tiles each CTA loads half of the B tile: K-major boxes are BN/2 rows tall
+  if (b_mn) e = make_map(&mb, B, K, N, ldb, 64, 64);
+  else e = make_map(&mb, B, N, K, ldb, 64, bn2 ? BN / 2 : BN);
   if (e) return e;
   GemmParams p;
   p.M = M; p.N = N; p.K = K;
@@ -558,6 +793,8 @@ int b200_gemm_bf16_rs(const void* A, int a_mn, long long lda, const void* B, int
     p.rs_seq = rs_seq;
   }
   cudaStream_t s = (cudaStream_t)stream;
+  if (bn2 == 256) return dispatch_major_2cta<256>(a_mn, b_mn, ma, mb, p, s);
+  if (bn2 == 128) return dispatch_major_2cta<128>(a_mn, b_mn, ma, mb, p, s);
   switch (BN) {
     case 16: return dispatch_major<16>(a_mn, b_mn, ma, mb, p, s);
     case 32: return dispatch_major<32>(a_mn, b_mn, ma, mb, p, s);
