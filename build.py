@@ -19,10 +19,12 @@ import sys
 from pathlib import Path
 
 ROOT = Path(__file__).resolve().parent
+EXTRA = os.environ.get("B200DP_NVCC_EXTRA", "").split()      # e.g. -DB200_MBAR_UNBOUNDED
+SUFFIX = os.environ.get("B200DP_LIB_SUFFIX", "")            # build a side-by-side variant
 PKG = "csed_514_project_distributed_training_using_pytorch_b200"
 SRC = ROOT / "csrc"
-OBJ = ROOT / "build" / "obj"
-OUT = ROOT / PKG / "lib" / "libb200dp.so"
+OBJ = ROOT / "build" / ("obj" + SUFFIX)
+OUT = ROOT / PKG / "lib" / f"libb200dp{SUFFIX}.so"
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
@@ -53,7 +55,7 @@ def compile_one(nvcc: str, src: Path, force: bool, verbose: bool, hdr_mtime: flo
     if (not force and obj.exists() and obj.stat().st_mtime >= src.stat().st_mtime
             and obj.stat().st_mtime >= hdr_mtime):
         return obj
-    cmd = [nvcc, *NVCC_FLAGS, "-c", str(src), "-o", str(obj)]
+    cmd = [nvcc, *NVCC_FLAGS, *EXTRA, "-c", str(src), "-o", str(obj)]
     if verbose:
         cmd.insert(1, "-Xptxas=-v")
         print(" ".join(cmd), flush=True)

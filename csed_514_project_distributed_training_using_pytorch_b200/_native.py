@@ -18,7 +18,8 @@ from pathlib import Path
 import torch
 
 _LIB = None
-_LIB_PATH = Path(__file__).resolve().parent / "lib" / "libb200dp.so"
+_LIB_PATH = Path(os.environ.get("B200DP_LIB") or
+                 (Path(__file__).resolve().parent / "lib" / "libb200dp.so"))
 
 c_p = C.c_void_p
 c_i = C.c_int

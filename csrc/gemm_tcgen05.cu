@@ -53,21 +53,30 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
                "r"(bytes)
                : "memory");
 }
-// Bounded: a protocol bug traps (CUDA error) after ~2 s instead of hanging the GPU.
+// Bounded: a protocol bug traps (CUDA error) instead of hanging the GPU. The wait passes a
+// 1 ms suspend-time hint so the four epilogue warps SLEEP on tmem_full during the main loop
+// instead of busy-polling (polling stole issue slots from the MMA thread: -13 % throughput);
+// the bound is an iteration count (~4 s), not a clock read per poll.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-  const long long t0 = clock64();
-  for (;;) {
-    uint32_t done;
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(done)
-        : "r"(smem_u32(bar)), "r"(parity)
-        : "memory");
-    if (done) return;
-    if (clock64() - t0 > 4000000000ll) __trap();
-  }
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p, q;\n\t.reg .u32 n;\n\t"
+      "mov.u32 n, 0;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, 1000000;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "add.u32 n, n, 1;\n\t"
+      "setp.lt.u32 q, n, 4096;\n\t"
+      "@q bra WAIT_%=;\n\t"
+      "mov.u32 %0, 0;\n\t"
+      "bra END_%=;\n\t"
+      "DONE_%=:\n\t"
+      "mov.u32 %0, 1;\n\t"
+      "END_%=:\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  if (!ok) __trap();
 }
 __device__ __forceinline__ void fence_barrier_init() {
   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -708,7 +717,7 @@ int use_2cta(int M, int N, bool rs_on) {
   static int mode = -1;
   if (mode < 0) {
     const char* e = getenv("B200DP_GEMM_2CTA");
-    mode = e ? (e[0] == '0' ? 0 : (e[0] == '1' ? 1 : 2)) : 2;
+    mode = e ? (e[0] == '0' ? 0 : (e[0] == '1' ? 1 : 2)) : 0;   // opt-in: see DESIGN.md 3b
   }
   if (mode == 0 || rs_on || N < 128 || M <= 128) return 0;
   const long long pairs256 = (long long)((M + 255) / 256) * ((N + 255) / 256);
