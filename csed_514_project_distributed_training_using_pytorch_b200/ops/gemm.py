@@ -18,7 +18,17 @@ N.register_sigs({
                        c_p, c_ll, c_p],
     "b200_gemm_bf16_rs": [c_p, c_i, c_ll, c_p, c_i, c_ll, c_p, c_i, c_ll, c_i, c_i, c_i, c_p, c_i,
                           c_p, c_ll, c_p, c_sz, c_sz, c_sz, c_sz, c_p, c_p],
+    "b200_gemm_set_variant": [c_i, c_i],
 })
+
+VARIANTS = {"auto": -1, "cta": 0, "pair": 1, "persistent": 2}
+
+
+def set_variant(kind="auto", bn: int = 0):
+    """Pin the GEMM kernel for tests / benchmarks: "cta" (one 128 x bn tile per CTA), "pair"
+    (one 256 x bn tile per CTA pair, cta_group::2), "persistent" (CTA pairs looping over
+    tiles with double-buffered TMEM) or "auto" (shape-based choice, the default)."""
+    N.call("b200_gemm_set_variant", VARIANTS[kind] if isinstance(kind, str) else int(kind), int(bn))
 
 
 def _chk(t: torch.Tensor, name: str):

@@ -24,6 +24,8 @@
 #include <cuda.h>
 #include <cuda_bf16.h>
 
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <unordered_map>
@@ -55,8 +57,10 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
 }
 // Bounded: a protocol bug traps (CUDA error) instead of hanging the GPU. The wait passes a
 // 1 ms suspend-time hint so the four epilogue warps SLEEP on tmem_full during the main loop
-// instead of busy-polling (polling stole issue slots from the MMA thread: -13 % throughput);
-// the bound is an iteration count (~4 s), not a clock read per poll.
+// instead of busy-polling (polling stole issue slots from the MMA thread: -13 % throughput).
+// The hardware returns from one suspended try_wait after ~0.5 us (ncu: ~380 iterations per
+// 200 us wait), so the bound of 2^22 iterations is ~2 s; it is an iteration count, not a
+// clock read per poll.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   uint32_t ok;
   asm volatile(
@@ -66,7 +70,7 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
       "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, 1000000;\n\t"
       "@p bra DONE_%=;\n\t"
       "add.u32 n, n, 1;\n\t"
-      "setp.lt.u32 q, n, 4096;\n\t"
+      "setp.lt.u32 q, n, 4194304;\n\t"
       "@q bra WAIT_%=;\n\t"
       "mov.u32 %0, 0;\n\t"
       "bra END_%=;\n\t"
@@ -77,6 +81,25 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
       : "r"(smem_u32(bar)), "r"(parity)
       : "memory");
   if (!ok) __trap();
+}
+// Wait used by the two single-thread roles (TMA producer, MMA issuer). Same as mbar_wait
+// unless built with -DB200_GEMM_SPIN (experiment: plain try_wait polling, no suspend hint).
+__device__ __forceinline__ void mbar_wait_role(uint64_t* bar, uint32_t parity) {
+#ifdef B200_GEMM_SPIN
+  uint32_t done = 0;
+  for (uint32_t n = 0; !done; ++n) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    if (n > (1u << 28)) __trap();
+  }
+#else
+  mbar_wait(bar, parity);
+#endif
 }
 __device__ __forceinline__ void fence_barrier_init() {
   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -206,7 +229,7 @@ template <int BN, bool B_MN> struct Cfg {
   // an MN-major B tile is made of whole 64-column boxes even when BN < 64
   static constexpr int B_BYTES = ((B_MN && BN < 64) ? 64 : BN) * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = (BN >= 128) ? 6 : 8;
+  static constexpr int STAGES = (BN >= 256) ? 4 : ((BN >= 128) ? 6 : 8);
   static constexpr int SMEM = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
   static constexpr int TMEM_COLS = BN < 32 ? 32 : BN;
 };
@@ -224,6 +247,9 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint8_t* tile
   const int lg = warp & 3;
   mbar_wait(tmem_full, 0);
   tcgen05_fence_after();
+#ifdef B200_GEMM_SKIP_EPI
+  return;   // experiment: main-loop time only
+#endif
   const int row = m0 + lg * 32 + lane;
   const bool row_ok = row < p.M;
   constexpr int CHUNK = BN >= 32 ? 32 : 16;
@@ -337,6 +363,106 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint8_t* tile
   }
 }
 
+// ===== epilogue of the persistent kernel: registers -> global, no shared memory =====
+// During the persistent main loop shared memory is saturated (TMA writes + tensor-core reads),
+// so this epilogue never touches it: each lane owns one accumulator row (tcgen05.ld 32x32b),
+// applies bias / ReLU / mask and stores 64-byte (bf16) or 128-byte (fp32) row pieces directly.
+// `release` is called once, as soon as the last TMEM read of the tile has landed in registers,
+// so the MMA warp can start the tile after next in this accumulator buffer.
+template <int BN, typename Release>
+__device__ __forceinline__ void epilogue_direct(const GemmParams& p, uint32_t tmem_acc, int warp,
+                                                int lane, int m0, int n0, Release release) {
+  const int lg = warp & 3;
+  const int row = m0 + lg * 32 + lane;
+  const bool row_ok = row < p.M;
+  const bool vec16 = (p.ldc % 8) == 0 && ((reinterpret_cast<uintptr_t>(p.C) & 15) == 0);
+#pragma unroll 1
+  for (int c0 = 0; c0 < BN; c0 += 32) {
+    uint32_t r[32];
+    tmem_ld32(tmem_acc + ((uint32_t)(lg * 32) << 16) + (uint32_t)c0, r);
+    tmem_ld_wait();
+    if (c0 + 32 >= BN) release();
+    const int col0 = n0 + c0;
+    if (col0 >= p.N) continue;
+    float v[32];
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+    const bool full_chunk = col0 + 32 <= p.N;
+    if (p.bias) {
+      if (full_chunk) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 8) {
+          const uint4 bv = *reinterpret_cast<const uint4*>(p.bias + col0 + j);
+          const uint32_t w[4] = {bv.x, bv.y, bv.z, bv.w};
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            v[j + 2 * q] += __uint_as_float(w[q] << 16);
+            v[j + 2 * q + 1] += __uint_as_float(w[q] & 0xffff0000u);
+          }
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (col0 + j < p.N) v[j] += __bfloat162float(p.bias[col0 + j]);
+      }
+    }
+    if (p.relu) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.0f);
+    }
+    if (!row_ok) continue;
+    if (p.relu_mask) {
+      const __nv_bfloat16* mrow = p.relu_mask + (size_t)row * p.ld_mask + col0;
+      if (full_chunk && (p.ld_mask % 8) == 0 && ((reinterpret_cast<uintptr_t>(p.relu_mask) & 15) == 0)) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 8) {
+          const uint4 mv = *reinterpret_cast<const uint4*>(mrow + j);
+          const uint32_t w[4] = {mv.x, mv.y, mv.z, mv.w};
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            if (__uint_as_float(w[q] << 16) <= 0.0f) v[j + 2 * q] = 0.0f;
+            if (__uint_as_float(w[q] & 0xffff0000u) <= 0.0f) v[j + 2 * q + 1] = 0.0f;
+          }
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (col0 + j < p.N && __bfloat162float(mrow[j]) <= 0.0f) v[j] = 0.0f;
+      }
+    }
+    if (p.c_fp32) {
+      float* crow = reinterpret_cast<float*>(p.C) + (size_t)row * p.ldc + col0;
+      if (full_chunk && (p.ldc % 4) == 0 && ((reinterpret_cast<uintptr_t>(p.C) & 15) == 0)) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 4)
+          *reinterpret_cast<float4*>(crow + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (col0 + j < p.N) crow[j] = v[j];
+      }
+    } else {
+      __nv_bfloat16* crow = reinterpret_cast<__nv_bfloat16*>(p.C) + (size_t)row * p.ldc + col0;
+      if (full_chunk && vec16) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 8) {
+          uint32_t w[4];
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const __nv_bfloat162 h = __floats2bfloat162_rn(v[j + 2 * q], v[j + 2 * q + 1]);
+            w[q] = *reinterpret_cast<const uint32_t*>(&h);
+          }
+          *reinterpret_cast<uint4*>(crow + j) = make_uint4(w[0], w[1], w[2], w[3]);
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (col0 + j < p.N) crow[j] = __float2bfloat16_rn(v[j]);
+      }
+    }
+  }
+}
+
 template <int BN, bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
@@ -392,7 +518,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
       for (int kb = 0; kb < num_kb; ++kb) {
         const int s = kb % C::STAGES;
         const uint32_t ph = (kb / C::STAGES) & 1;
-        mbar_wait(&empty[s], ph ^ 1);
+        mbar_wait_role(&empty[s], ph ^ 1);
         uint8_t* a_dst = tiles + s * C::STAGE_BYTES;
         uint8_t* b_dst = a_dst + C::A_BYTES;
         mbar_expect_tx(&full[s], C::STAGE_BYTES);
@@ -419,7 +545,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
       for (int kb = 0; kb < num_kb; ++kb) {
         const int s = kb % C::STAGES;
         const uint32_t ph = (kb / C::STAGES) & 1;
-        mbar_wait(&full[s], ph);
+        mbar_wait_role(&full[s], ph);
         tcgen05_fence_after();
         const uint32_t a_addr = smem_u32(tiles + s * C::STAGE_BYTES);
         const uint32_t b_addr = a_addr + C::A_BYTES;
@@ -455,7 +581,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a,
 // 256 output rows instead of once per 128: the L2 -> SM operand traffic that caps the 1-CTA
 // kernel at ~47 % tensor-pipe activity is cut by a quarter (BN=128) to a half (BN=256).
 //   * both CTAs issue their TMA loads with .cta_group::2 and complete them on the LEADER's
-//     `full` barrier (address obtained with mapa); the peer also arrives there remotely
+//     `full` barrier (address obtained with mapa), which the leader's producer arms with the
+//     byte count of both CTAs (the peer never touches the barrier itself)
 //   * only the leader's elected thread issues the MMAs; tcgen05.commit ... multicast::cluster
 //     releases the stage in both CTAs and finally raises tmem_full in both
 //   * each CTA drains its own 128 TMEM lanes with the common epilogue
@@ -474,11 +601,11 @@ __device__ __forceinline__ uint32_t mapa_shared(uint32_t local_addr, uint32_t ct
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_addr), "r"(cta_rank));
   return r;
 }
-__device__ __forceinline__ void mbar_expect_tx_cluster(uint32_t cluster_addr, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.release.cluster.shared::cluster.b64 _, [%0], %1;" ::"r"(
-                   cluster_addr),
-               "r"(bytes)
-               : "memory");
+// Arrive on a barrier of another CTA of the cluster (address from mapa). Default semantics
+// (release at CTA scope): an explicit .release.cluster here compiles to MEMBAR.ALL.GPU + ERRBAR,
+// which serialised the producer loop of the first 2-CTA kernel (ncu: 0.62 PFLOP/s).
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 __device__ __forceinline__ void tma_load_2d_2sm(void* dst, const CUtensorMap* map,
                                                 uint32_t leader_bar_cluster_addr, int c0, int c1) {
@@ -551,7 +678,7 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap map_a,
     tma_prefetch_desc(&map_a);
     tma_prefetch_desc(&map_b);
     for (int s = 0; s < C::STAGES; ++s) {
-      mbar_init(&full[s], 2);     // one arrive.expect_tx from each CTA's producer (leader's copy is used)
+      mbar_init(&full[s], 1);     // the leader's producer arms it with the bytes of BOTH CTAs
       mbar_init(&empty[s], 1);    // one multicast commit from the leader's MMA thread
     }
     mbar_init(tmem_full, 1);
@@ -571,11 +698,11 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap map_a,
       for (int kb = 0; kb < num_kb; ++kb) {
         const int s = kb % C::STAGES;
         const uint32_t ph = (kb / C::STAGES) & 1;
-        mbar_wait(&empty[s], ph ^ 1);
+        mbar_wait_role(&empty[s], ph ^ 1);
         uint8_t* a_dst = tiles + s * C::STAGE_BYTES;
         uint8_t* b_dst = a_dst + C::A_BYTES;
         const uint32_t lead_full = mapa_shared(smem_u32(&full[s]), 0);
-        mbar_expect_tx_cluster(lead_full, C::STAGE_BYTES);
+        if (rank == 0) mbar_expect_tx(&full[s], 2 * C::STAGE_BYTES);
         const int k0 = kb * BK;
         if (A_MN) {
           tma_load_2d_2sm(a_dst, &map_a, lead_full, m0, k0);
@@ -599,7 +726,7 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap map_a,
       for (int kb = 0; kb < num_kb; ++kb) {
         const int s = kb % C::STAGES;
         const uint32_t ph = (kb / C::STAGES) & 1;
-        mbar_wait(&full[s], ph);
+        mbar_wait_role(&full[s], ph);
         tcgen05_fence_after();
         const uint32_t a_addr = smem_u32(tiles + s * C::STAGE_BYTES);
         const uint32_t b_addr = a_addr + C::A_BYTES;
@@ -617,6 +744,159 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap map_a,
     }
   } else {
     epilogue_tile<BN>(p, tiles, tmem_full, tmem_base, warp, lane, m0, n0);
+  }
+  tcgen05_fence_before();
+  cluster_sync_all();            // nobody frees TMEM or exits while the peer still depends on it
+  if (warp == 1) {
+    tcgen05_fence_after();
+    tmem_dealloc_2sm(tmem_base, C::TMEM_COLS);
+  }
+}
+
+// ===========================================================================
+// Persistent 2-CTA kernel: one cluster (CTA pair) per TPC loops over 256 x BN output tiles.
+// TMEM holds TWO accumulator buffers (2 x BN columns), so the four epilogue warps of each CTA
+// drain tile i (tcgen05.ld -> registers -> global) while the MMA thread is already running
+// the main loop of tile i+1; the smem ring, its phases and the TMA producer simply keep
+// running across tile boundaries. Three pipelines:
+//   full/empty[STAGES]   TMA <-> MMA   (as in the one-tile 2-CTA kernel)
+//   tmem_full[2]         MMA -> epilogue, multicast commit to both CTAs
+//   tmem_empty[2]        epilogue -> MMA, on the LEADER: 4 warps x 2 CTAs arrive (the peer's
+//                        warps arrive remotely through mapa)
+// Tiles are assigned round-robin (tile = cluster + i * clusters, M fastest), so the ~74 tiles
+// in flight share a few column blocks of B and all of A through L2.
+// ===========================================================================
+template <int BN, bool B_MN> struct CfgP {
+  static constexpr int A_BYTES = BM * BK * 2;              // this CTA's 128 rows
+  static constexpr int B_BYTES = (BN / 2) * BK * 2;        // this CTA's half of the columns
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int STAGES = (BN >= 256) ? 6 : 8;       // 192 KB either way
+  static constexpr int SMEM = STAGES * STAGE_BYTES + 1024 + 256;
+  static constexpr int TMEM_COLS = 2 * BN;                 // double-buffered accumulator
+};
+
+template <int BN, bool A_MN, bool B_MN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
+gemm_bf16_tcgen05_persist_kernel(const __grid_constant__ CUtensorMap map_a,
+                                 const __grid_constant__ CUtensorMap map_b, GemmParams p) {
+  using C = CfgP<BN, B_MN>;
+  static_assert(BN == 128 || BN == 256, "2-CTA tiles are 256x128 or 256x256");
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~(uintptr_t)1023);
+  uint8_t* tiles = smem;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + C::STAGES * C::STAGE_BYTES);
+  uint64_t* empty = full + C::STAGES;
+  uint64_t* tmem_full = empty + C::STAGES;       // [2]
+  uint64_t* tmem_empty = tmem_full + 2;          // [2], the leader's copy is the one in use
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();                 // 0 = leader
+  const int cluster_id = blockIdx.x >> 1, num_clusters = gridDim.x >> 1;
+  const int tiles_m = (p.M + 255) / 256;
+  const int num_tiles = tiles_m * ((p.N + BN - 1) / BN);
+  const int num_kb = (p.K + BK - 1) / BK;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&map_a);
+    tma_prefetch_desc(&map_b);
+    for (int s = 0; s < C::STAGES; ++s) {
+      mbar_init(&full[s], 1);     // armed by the leader's producer with the bytes of both CTAs
+      mbar_init(&empty[s], 1);    // one multicast commit from the leader's MMA thread
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&tmem_full[b], 1);
+      mbar_init(&tmem_empty[b], 8);   // 4 epilogue warps in each of the two CTAs
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc_2sm(tmem_slot, C::TMEM_COLS);
+  pdl_trigger();
+  tcgen05_fence_before();
+  cluster_sync_all();            // both CTAs' barriers and TMEM are ready before anyone signals
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();
+
+  if (warp == 0) {
+    // ===== TMA producer (both CTAs): the ring keeps rolling across tiles =====
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int t = cluster_id; t < num_tiles; t += num_clusters) {
+        const int m0 = (t % tiles_m) * 256 + (int)rank * BM;
+        const int nb0 = (t / tiles_m) * BN + (int)rank * (BN / 2);
+        for (int kb = 0; kb < num_kb; ++kb, ++it) {
+          const uint32_t s = it % C::STAGES;
+          const uint32_t ph = (it / C::STAGES) & 1;
+          mbar_wait_role(&empty[s], ph ^ 1);
+          uint8_t* a_dst = tiles + s * C::STAGE_BYTES;
+          uint8_t* b_dst = a_dst + C::A_BYTES;
+          const uint32_t lead_full = mapa_shared(smem_u32(&full[s]), 0);
+          if (rank == 0) mbar_expect_tx(&full[s], 2 * C::STAGE_BYTES);
+          const int k0 = kb * BK;
+          if (A_MN) {
+            tma_load_2d_2sm(a_dst, &map_a, lead_full, m0, k0);
+            tma_load_2d_2sm(a_dst + BK * 128, &map_a, lead_full, m0 + 64, k0);
+          } else {
+            tma_load_2d_2sm(a_dst, &map_a, lead_full, k0, m0);
+          }
+          if (B_MN) {
+#pragma unroll
+            for (int j = 0; j < BN / 2 / 64; ++j)
+              tma_load_2d_2sm(b_dst + j * BK * 128, &map_b, lead_full, nb0 + 64 * j, k0);
+          } else {
+            tma_load_2d_2sm(b_dst, &map_b, lead_full, k0, nb0);
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer (leader CTA only) =====
+    if (rank == 0 && lane == 0) {
+      constexpr uint32_t idesc = make_idesc(256, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
+      uint32_t it = 0, tcount = 0;
+      for (int t = cluster_id; t < num_tiles; t += num_clusters, ++tcount) {
+        const uint32_t buf = tcount & 1, use = tcount >> 1;
+        mbar_wait_role(&tmem_empty[buf], (use & 1) ^ 1);    // both CTAs drained this buffer
+        tcgen05_fence_after();
+        const uint32_t acc = tmem_base + buf * BN;
+        for (int kb = 0; kb < num_kb; ++kb, ++it) {
+          const uint32_t s = it % C::STAGES;
+          const uint32_t ph = (it / C::STAGES) & 1;
+          mbar_wait_role(&full[s], ph);
+          tcgen05_fence_after();
+          const uint32_t a_addr = smem_u32(tiles + s * C::STAGE_BYTES);
+          const uint32_t b_addr = a_addr + C::A_BYTES;
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            const uint64_t adesc = A_MN ? make_smem_desc(a_addr + k * UMMA_K * 128, BK * 128, 1024)
+                                        : make_smem_desc(a_addr + k * UMMA_K * 2, 16, 1024);
+            const uint64_t bdesc = B_MN ? make_smem_desc(b_addr + k * UMMA_K * 128, BK * 128, 1024)
+                                        : make_smem_desc(b_addr + k * UMMA_K * 2, 16, 1024);
+            umma_bf16_2sm(acc, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+          }
+          umma_commit_2sm(&empty[s]);        // frees the stage in BOTH CTAs
+        }
+        umma_commit_2sm(&tmem_full[buf]);    // this accumulator is complete in both CTAs
+      }
+    }
+  } else {
+    // ===== epilogue warps (both CTAs) =====
+    const uint32_t lead_empty0 = mapa_shared(smem_u32(&tmem_empty[0]), 0);
+    uint32_t tcount = 0;
+    for (int t = cluster_id; t < num_tiles; t += num_clusters, ++tcount) {
+      const uint32_t buf = tcount & 1, use = tcount >> 1;
+      const int m0 = (t % tiles_m) * 256 + (int)rank * BM;
+      const int n0 = (t / tiles_m) * BN;
+      mbar_wait(&tmem_full[buf], use & 1);
+      tcgen05_fence_after();
+      epilogue_direct<BN>(p, tmem_base + buf * BN, warp, lane, m0, n0, [&]() {
+        tcgen05_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(lead_empty0 + buf * 8);
+      });
+    }
   }
   tcgen05_fence_before();
   cluster_sync_all();            // nobody frees TMEM or exits while the peer still depends on it
@@ -711,20 +991,78 @@ int dispatch_major_2cta(int a_mn, int b_mn, const CUtensorMap& ma, const CUtenso
   return launch_2cta<BN, true, false>(ma, mb, p, s);
 }
 
-// 2-CTA tiles are used when the problem is big enough to fill the machine with 256-row
-// pairs (B200DP_GEMM_2CTA=0 disables, =1 forces whenever the shape allows).
-int use_2cta(int M, int N, bool rs_on) {
-  static int mode = -1;
-  if (mode < 0) {
-    const char* e = getenv("B200DP_GEMM_2CTA");
-    mode = e ? (e[0] == '0' ? 0 : (e[0] == '1' ? 1 : 2)) : 0;   // opt-in: see DESIGN.md 3b
+template <int BN, bool A_MN, bool B_MN>
+int launch_persist(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p, cudaStream_t s) {
+  using C = CfgP<BN, B_MN>;
+  auto kern = gemm_bf16_tcgen05_persist_kernel<BN, A_MN, B_MN>;
+  static bool attr_done[64] = {false};
+  static int sms[64] = {0};
+  int dev = 0;
+  B200_CUDA_OK(cudaGetDevice(&dev));
+  if (!attr_done[dev & 63]) {
+    B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM));
+    B200_CUDA_OK(cudaDeviceGetAttribute(&sms[dev & 63], cudaDevAttrMultiProcessorCount, dev));
+    attr_done[dev & 63] = true;
   }
-  if (mode == 0 || rs_on || N < 128 || M <= 128) return 0;
-  const long long pairs256 = (long long)((M + 255) / 256) * ((N + 255) / 256);
-  if (N >= 256 && (mode == 1 || pairs256 * 2 >= 120)) return 256;
-  const long long pairs128 = (long long)((M + 255) / 256) * ((N + 127) / 128);
-  if (mode == 1 || pairs128 * 2 >= 100) return 128;
+  const int tiles = ((p.M + 255) / 256) * ((p.N + BN - 1) / BN);
+  int clusters = sms[dev & 63] / 2;                 // one CTA pair per TPC
+  if (clusters > tiles) clusters = tiles;
+  // same makespan with fewer pairs when the last wave would be ragged (less L2 contention)
+  const int waves = (tiles + clusters - 1) / clusters;
+  clusters = (tiles + waves - 1) / waves;
+  B200_CUDA_OK(b200_launch_pdl(kern, dim3(2 * clusters), dim3(GEMM_THREADS), (size_t)C::SMEM, s,
+                               b200_pdl_enabled() != 0, ma, mb, p));
   return 0;
+}
+
+template <int BN>
+int dispatch_major_persist(int a_mn, int b_mn, const CUtensorMap& ma, const CUtensorMap& mb,
+                           const GemmParams& p, cudaStream_t s) {
+  if (!a_mn && !b_mn) return launch_persist<BN, false, false>(ma, mb, p, s);
+  if (!a_mn && b_mn) return launch_persist<BN, false, true>(ma, mb, p, s);
+  if (a_mn && b_mn) return launch_persist<BN, true, true>(ma, mb, p, s);
+  return launch_persist<BN, true, false>(ma, mb, p, s);
+}
+
+// Kernel choice. kind 0: one 128 x BN tile per CTA; 1: one 256 x BN tile per CTA pair;
+// 2: persistent CTA pairs with double-buffered TMEM. b200_gemm_set_variant (or
+// B200DP_GEMM_VARIANT=kind[,bn]) pins the kind (and optionally BN) for tests and benchmarks;
+// -1 = automatic.
+struct Plan { int kind, bn; };
+int g_force_kind = -2, g_force_bn = 0;
+
+Plan choose(int M, int N, bool rs_on) {
+  if (g_force_kind == -2) {
+    g_force_kind = -1;
+    if (const char* e = getenv("B200DP_GEMM_VARIANT")) {
+      int k = -1, bn = 0;
+      if (sscanf(e, "%d,%d", &k, &bn) >= 1) { g_force_kind = k; g_force_bn = bn; }
+    }
+  }
+  const int small_bn = (N <= 16) ? 16 : (N <= 32 ? 32 : (N <= 64 ? 64 : 128));
+  const bool pair_ok = !rs_on && N >= 128 && M > 128;
+  if (g_force_kind >= 0) {
+    if (g_force_kind >= 1 && pair_ok) {
+      int bn = g_force_bn ? g_force_bn : (N >= 256 ? 256 : 128);
+      if (bn != 128 && bn != 256) bn = 256;
+      if (N < bn) bn = 128;
+      return {g_force_kind > 2 ? 2 : g_force_kind, bn};
+    }
+    int bn = g_force_bn ? g_force_bn : small_bn;
+    if (bn == 256 && (N < 256 || rs_on)) bn = small_bn;
+    if (bn != 16 && bn != 32 && bn != 64 && bn != 128 && bn != 256) bn = small_bn;
+    if (bn > small_bn && bn != 256) bn = small_bn;
+    return {0, bn};
+  }
+  // automatic
+  if (pair_ok) {
+    const long long t256 = (long long)((M + 255) / 256) * ((N + 255) / 256);
+    if (N >= 256 && t256 >= 56) return {2, 256};
+    const long long t128 = (long long)((M + 255) / 256) * ((N + 127) / 128);
+    if (t128 >= 56) return {2, 128};
+  }
+  if (!rs_on && N >= 256 && (long long)((M + 127) / 128) * ((N + 255) / 256) >= 120) return {0, 256};
+  return {0, small_bn};
 }
 
 template <int BN>
@@ -754,6 +1092,13 @@ int b200_gemm_bf16_rs(const void* A, int a_mn, long long lda, const void* B, int
                       size_t rs_slice_vec, size_t rs_base_vec, const unsigned* rs_seq,
                       void* stream);
 
+// Pin the kernel kind / tile width (see choose()); kind = -1 restores the automatic choice.
+int b200_gemm_set_variant(int kind, int bn) {
+  g_force_kind = kind < 0 ? -1 : kind;
+  g_force_bn = kind < 0 ? 0 : bn;
+  return 0;
+}
+
 int b200_gemm_bf16(const void* A, int a_mn, long long lda, const void* B, int b_mn, long long ldb,
                    void* C, int c_fp32, long long ldc, int M, int N, int K, const void* bias,
                    int relu, const void* relu_mask, long long ld_mask, void* stream) {
@@ -772,8 +1117,9 @@ int b200_gemm_bf16_rs(const void* A, int a_mn, long long lda, const void* B, int
                       size_t rs_slice_vec, size_t rs_base_vec, const unsigned* rs_seq,
                       void* stream) {
   B200_REQUIRE(M > 0 && N > 0 && K > 0, "b200_gemm_bf16: empty problem");
-  const int bn2 = use_2cta(M, N, rs_comm != nullptr);
-  const int BN = bn2 ? bn2 : ((N <= 16) ? 16 : (N <= 32 ? 32 : (N <= 64 ? 64 : 128)));
+  const Plan plan = choose(M, N, rs_comm != nullptr);
+  const int BN = plan.bn;
+  const int bn2 = plan.kind ? plan.bn : 0;      // CTA-pair kernels: each CTA loads half of the B tile
   CUtensorMap ma, mb;
   int e;
   if (a_mn) e = make_map(&ma, A, K, M, lda, 64, 64); else e = make_map(&ma, A, M, K, lda, 64, BM);
@@ -802,12 +1148,17 @@ int b200_gemm_bf16_rs(const void* A, int a_mn, long long lda, const void* B, int
     p.rs_seq = rs_seq;
   }
   cudaStream_t s = (cudaStream_t)stream;
-  if (bn2 == 256) return dispatch_major_2cta<256>(a_mn, b_mn, ma, mb, p, s);
-  if (bn2 == 128) return dispatch_major_2cta<128>(a_mn, b_mn, ma, mb, p, s);
+  if (plan.kind == 2)
+    return BN == 256 ? dispatch_major_persist<256>(a_mn, b_mn, ma, mb, p, s)
+                     : dispatch_major_persist<128>(a_mn, b_mn, ma, mb, p, s);
+  if (plan.kind == 1)
+    return BN == 256 ? dispatch_major_2cta<256>(a_mn, b_mn, ma, mb, p, s)
+                     : dispatch_major_2cta<128>(a_mn, b_mn, ma, mb, p, s);
   switch (BN) {
     case 16: return dispatch_major<16>(a_mn, b_mn, ma, mb, p, s);
     case 32: return dispatch_major<32>(a_mn, b_mn, ma, mb, p, s);
     case 64: return dispatch_major<64>(a_mn, b_mn, ma, mb, p, s);
+    case 256: return dispatch_major<256>(a_mn, b_mn, ma, mb, p, s);
     default: return dispatch_major<128>(a_mn, b_mn, ma, mb, p, s);
   }
 }

@@ -169,6 +169,10 @@ int b200_gemm_bf16_rs(const void* A, int a_mn, long long lda, const void* B, int
                       const void* rs_comm, size_t rs_stage_off, size_t rs_src_bytes,
                       size_t rs_slice_vec, size_t rs_base_vec, const unsigned* rs_seq,
                       void* stream);
+/* Pin the GEMM kernel: kind 0 = one 128 x bn tile per CTA (bn 16..256), 1 = one 256 x bn tile
+ * per CTA pair (cta_group::2), 2 = persistent CTA pairs with double-buffered TMEM; bn 0 = pick.
+ * kind -1 restores the automatic choice (also: env B200DP_GEMM_VARIANT=kind[,bn]). */
+int b200_gemm_set_variant(int kind, int bn);
 /* conv2 forward as a TF32 implicit GEMM on tcgen05 (same contract as b200_conv2_fwd). */
 int b200_conv2_fwd_tc(const float* a1, const float* w, const float* b, float* mask, int mask_mode,
                       float p, unsigned long long seed, unsigned long long step, float* a2,

@@ -51,3 +51,51 @@ def test_gemm_epilogues(cuda_device):
     gemm.gemm_bf16(dy, x, True, True, out=big[:, :K])
     torch.testing.assert_close(big[:, :K], want_dW, rtol=2e-3, atol=2e-2)
     assert torch.count_nonzero(big[:, K:]) == 0
+
+
+@pytest.fixture
+def restore_variant():
+    yield
+    gemm.set_variant("auto")
+
+
+# (kind, bn): the one-tile kernel at its widest tile, the CTA-pair kernel, the persistent kernel
+_VARIANTS = [("cta", 256), ("pair", 256), ("pair", 128), ("persistent", 256), ("persistent", 128)]
+
+
+@pytest.mark.parametrize("kind,bn", _VARIANTS)
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, True), (True, False)])
+@pytest.mark.parametrize("M,N,K", [(512, 512, 256), (304, 264, 520), (1024, 384, 72)])
+def test_gemm_variants(cuda_device, restore_variant, kind, bn, a_mn, b_mn, M, N, K):
+    g = torch.Generator().manual_seed(M + 3 * N + 5 * K)
+    A = torch.randn((K, M) if a_mn else (M, K), generator=g).to(torch.bfloat16).to(cuda_device)
+    B = torch.randn((K, N) if b_mn else (N, K), generator=g).to(torch.bfloat16).to(cuda_device)
+    want = _ref(A, B, a_mn, b_mn)
+    gemm.set_variant(kind, bn)
+    got32 = gemm.gemm_bf16(A, B, a_mn, b_mn, out_dtype=torch.float32)
+    torch.testing.assert_close(got32, want, rtol=2e-3, atol=2e-2 * (K ** 0.5) / 8)
+    got16 = gemm.gemm_bf16(A, B, a_mn, b_mn)
+    torch.testing.assert_close(got16.float(), want, rtol=1.6e-2, atol=2e-2 * (K ** 0.5) / 4)
+
+
+@pytest.mark.parametrize("kind,bn", [("persistent", 256), ("persistent", 128), ("pair", 256)])
+def test_gemm_many_tiles_per_cluster(cuda_device, restore_variant, kind, bn):
+    """More tiles than CTA pairs: every pair walks several tiles, so the TMEM double buffer,
+    the barrier phases and the smem ring wrap around (K = 3 blocks against 6-8 stages)."""
+    g = torch.Generator().manual_seed(11)
+    M, N, K = 4096 + 40, 4096 + 24, 192
+    x = (torch.randn(M, K, generator=g)).to(torch.bfloat16).to(cuda_device)
+    W = (torch.randn(N, K, generator=g)).to(torch.bfloat16).to(cuda_device)
+    b = torch.randn(N, generator=g).to(torch.bfloat16).to(cuda_device)
+    gemm.set_variant(kind, bn)
+    y = gemm.linear_fwd(x, W, b, relu=True)
+    want = torch.relu(x.float() @ W.float().t() + b.float())
+    torch.testing.assert_close(y.float(), want, rtol=1.6e-2, atol=8e-2)
+    act = torch.randn(M, K, generator=g).to(torch.bfloat16).to(cuda_device)
+    dy = torch.randn(M, N, generator=g).to(torch.bfloat16).to(cuda_device)
+    dx = gemm.linear_dgrad(dy, W, relu_mask=act)      # output is 192 wide: 128-column tiles, 65 K blocks
+    want_dx = (dy.float() @ W.float()) * (act.float() > 0)
+    torch.testing.assert_close(dx.float(), want_dx, rtol=1.6e-2, atol=0.6)
+    dW = gemm.linear_wgrad(dy[:, :512].contiguous(), dy[:, 512:1024].contiguous())
+    want_dW = dy[:, :512].float().t() @ dy[:, 512:1024].float()
+    torch.testing.assert_close(dW.float(), want_dW, rtol=1.6e-2, atol=0.6)
