@@ -234,6 +234,54 @@ template <int BN, bool B_MN> struct Cfg {
   static constexpr int TMEM_COLS = BN < 32 ? 32 : BN;
 };
 
+// Second half of a staged bf16 epilogue: the warp's 32 rows sit in shared memory
+// (PITCH = BN*2+16 bytes apart); every store instruction now covers whole 16-byte-vector rows
+// (512 contiguous bytes for BN = 256), either to C or, with the reduce-scatter epilogue, to the
+// staging slot of the rank that owns that slice of the gradient bucket over NVLink.
+template <int BN>
+__device__ __forceinline__ void store_staged_rows(const GemmParams& p, const uint8_t* sbuf, int lg,
+                                                  int lane, int m0, int n0) {
+  constexpr int PITCH = BN * 2 + 16;
+  constexpr int VPR = BN / 8;                   // 16-byte vectors per tile row
+  constexpr int RPI = 32 / VPR;                 // rows written per warp-wide store
+  const int cv = lane % VPR;
+  const int col = n0 + cv * 8;
+  const bool vec_ok = (p.ldc % 8) == 0 && ((reinterpret_cast<uintptr_t>(p.C) & 15) == 0);
+  unsigned slot = 0;
+  size_t slot_vec = 0;
+  if (p.rs_on) {
+    slot = (*p.rs_seq + 1u) & 1u;
+    slot_vec = (size_t)p.rs_comm.world * p.rs_src_vec;
+  }
+#pragma unroll 1
+  for (int it = 0; it < VPR; ++it) {           // 32 rows / RPI rows per iteration == VPR
+    const int rl = it * RPI + lane / VPR;
+    const int grow = m0 + lg * 32 + rl;
+    if (grow >= p.M || col >= p.N) continue;
+    const uint4 val = *reinterpret_cast<const uint4*>(sbuf + rl * PITCH + cv * 16);
+    if (p.rs_on) {
+      // reduce-scatter epilogue: vector `vec` of the bucket goes to owner vec / sl
+      if (col + 8 <= p.N) {
+        const size_t vec = p.rs_base_vec + ((size_t)grow * p.ldc + col) / 8;
+        const int owner = (int)(vec / p.rs_sl);
+        uint4* dst = peer_ptr<uint4>(p.rs_comm, owner, p.rs_stage_off) + slot * slot_vec +
+                     (size_t)p.rs_comm.rank * p.rs_src_vec + (vec - (size_t)owner * p.rs_sl);
+        *dst = val;
+      }
+    } else {
+      __nv_bfloat16* cptr = reinterpret_cast<__nv_bfloat16*>(p.C) + (size_t)grow * p.ldc + col;
+      if (vec_ok && col + 8 <= p.N) {
+        *reinterpret_cast<uint4*>(cptr) = val;
+      } else {
+        const __nv_bfloat16* sv = reinterpret_cast<const __nv_bfloat16*>(&val);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (col + j < p.N) cptr[j] = sv[j];
+      }
+    }
+  }
+}
+
 // ===== epilogue (shared by the 1-CTA and the 2-CTA kernels): warps 2..5 =====
 template <int BN>
 __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint8_t* tiles,
@@ -322,44 +370,7 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint8_t* tile
   }
   if (!p.c_fp32) {
     __syncwarp();
-    constexpr int VPR = BN / 8;                   // 16-byte vectors per tile row
-    constexpr int RPI = 32 / VPR;                 // rows written per warp-wide store
-    const int cv = lane % VPR;
-    const int col = n0 + cv * 8;
-    const bool vec_ok = (p.ldc % 8) == 0 && ((reinterpret_cast<uintptr_t>(p.C) & 15) == 0);
-    unsigned slot = 0;
-    size_t slot_vec = 0;
-    if (p.rs_on) {
-      slot = (*p.rs_seq + 1u) & 1u;
-      slot_vec = (size_t)p.rs_comm.world * p.rs_src_vec;
-    }
-#pragma unroll 1
-    for (int it = 0; it < VPR; ++it) {           // 32 rows / RPI rows per iteration == VPR
-      const int rl = it * RPI + lane / VPR;
-      const int grow = m0 + lg * 32 + rl;
-      if (grow >= p.M || col >= p.N) continue;
-      const uint4 val = *reinterpret_cast<const uint4*>(sbuf + rl * PITCH + cv * 16);
-      if (p.rs_on) {
-        // reduce-scatter epilogue: vector `vec` of the bucket goes to owner vec / sl
-        if (col + 8 <= p.N) {
-          const size_t vec = p.rs_base_vec + ((size_t)grow * p.ldc + col) / 8;
-          const int owner = (int)(vec / p.rs_sl);
-          uint4* dst = peer_ptr<uint4>(p.rs_comm, owner, p.rs_stage_off) + slot * slot_vec +
-                       (size_t)p.rs_comm.rank * p.rs_src_vec + (vec - (size_t)owner * p.rs_sl);
-          *dst = val;
-        }
-      } else {
-        __nv_bfloat16* cptr = reinterpret_cast<__nv_bfloat16*>(p.C) + (size_t)grow * p.ldc + col;
-        if (vec_ok && col + 8 <= p.N) {
-          *reinterpret_cast<uint4*>(cptr) = val;
-        } else {
-          const __nv_bfloat16* sv = reinterpret_cast<const __nv_bfloat16*>(&val);
-#pragma unroll
-          for (int j = 0; j < 8; ++j)
-            if (col + j < p.N) cptr[j] = sv[j];
-        }
-      }
-    }
+    store_staged_rows<BN>(p, sbuf, lg, lane, m0, n0);
   }
 }
 
@@ -461,6 +472,40 @@ __device__ __forceinline__ void epilogue_direct(const GemmParams& p, uint32_t tm
       }
     }
   }
+}
+
+// Reduce-scatter epilogue of the persistent kernel (wgrad of a data-parallel layer). The
+// stores cross NVLink, where 512-byte coalescing matters more than shared-memory bandwidth,
+// so the bf16 tile rows are staged in a dedicated shared-memory area (the kernel then runs
+// with a shorter operand ring) and pushed to the owner ranks row by row.
+template <int BN, typename Release>
+__device__ __forceinline__ void epilogue_rs_staged(const GemmParams& p, uint8_t* stage,
+                                                   uint32_t tmem_acc, int warp, int lane, int m0,
+                                                   int n0, Release release) {
+  constexpr int PITCH = BN * 2 + 16;
+  const int lg = warp & 3;
+  uint8_t* sbuf = stage + lg * (32 * PITCH);
+#pragma unroll 1
+  for (int c0 = 0; c0 < BN; c0 += 32) {
+    uint32_t r[32];
+    tmem_ld32(tmem_acc + ((uint32_t)(lg * 32) << 16) + (uint32_t)c0, r);
+    tmem_ld_wait();
+    if (c0 + 32 >= BN) release();
+#pragma unroll
+    for (int j = 0; j < 32; j += 8) {
+      uint32_t w[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const __nv_bfloat162 h = __floats2bfloat162_rn(__uint_as_float(r[j + 2 * q]),
+                                                       __uint_as_float(r[j + 2 * q + 1]));
+        w[q] = *reinterpret_cast<const uint32_t*>(&h);
+      }
+      *reinterpret_cast<uint4*>(sbuf + lane * PITCH + (c0 + j) * 2) = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+  }
+  __syncwarp();
+  store_staged_rows<BN>(p, sbuf, lg, lane, m0, n0);
+  __syncwarp();                 // the next tile overwrites the staging rows
 }
 
 template <int BN, bool A_MN, bool B_MN>
@@ -766,26 +811,29 @@ gemm_bf16_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap map_a,
 // Tiles are assigned round-robin (tile = cluster + i * clusters, M fastest), so the ~74 tiles
 // in flight share a few column blocks of B and all of A through L2.
 // ===========================================================================
-template <int BN, bool B_MN> struct CfgP {
+template <int BN, bool B_MN, bool RS> struct CfgP {
   static constexpr int A_BYTES = BM * BK * 2;              // this CTA's 128 rows
   static constexpr int B_BYTES = (BN / 2) * BK * 2;        // this CTA's half of the columns
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = (BN >= 256) ? 6 : 8;       // 192 KB either way
-  static constexpr int SMEM = STAGES * STAGE_BYTES + 1024 + 256;
+  // 192 KB of operand ring; the reduce-scatter epilogue trades two stages for row staging
+  static constexpr int STAGES = (BN >= 256) ? (RS ? 4 : 6) : (RS ? 6 : 8);
+  static constexpr int EPI_BYTES = RS ? 4 * 32 * (BN * 2 + 16) : 0;
+  static constexpr int SMEM = STAGES * STAGE_BYTES + EPI_BYTES + 1024 + 256;
   static constexpr int TMEM_COLS = 2 * BN;                 // double-buffered accumulator
 };
 
-template <int BN, bool A_MN, bool B_MN>
+template <int BN, bool A_MN, bool B_MN, bool RS>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_tcgen05_persist_kernel(const __grid_constant__ CUtensorMap map_a,
                                  const __grid_constant__ CUtensorMap map_b, GemmParams p) {
-  using C = CfgP<BN, B_MN>;
+  using C = CfgP<BN, B_MN, RS>;
   static_assert(BN == 128 || BN == 256, "2-CTA tiles are 256x128 or 256x256");
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~(uintptr_t)1023);
   uint8_t* tiles = smem;
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + C::STAGES * C::STAGE_BYTES);
+  uint8_t* epi_stage = smem + C::STAGES * C::STAGE_BYTES;
+  uint64_t* full = reinterpret_cast<uint64_t*>(epi_stage + C::EPI_BYTES);
   uint64_t* empty = full + C::STAGES;
   uint64_t* tmem_full = empty + C::STAGES;       // [2]
   uint64_t* tmem_empty = tmem_full + 2;          // [2], the leader's copy is the one in use
@@ -891,11 +939,15 @@ gemm_bf16_tcgen05_persist_kernel(const __grid_constant__ CUtensorMap map_a,
       const int n0 = (t / tiles_m) * BN;
       mbar_wait(&tmem_full[buf], use & 1);
       tcgen05_fence_after();
-      epilogue_direct<BN>(p, tmem_base + buf * BN, warp, lane, m0, n0, [&]() {
+      auto release = [&]() {
         tcgen05_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive_cluster(lead_empty0 + buf * 8);
-      });
+      };
+      if constexpr (RS)
+        epilogue_rs_staged<BN>(p, epi_stage, tmem_base + buf * BN, warp, lane, m0, n0, release);
+      else
+        epilogue_direct<BN>(p, tmem_base + buf * BN, warp, lane, m0, n0, release);
     }
   }
   tcgen05_fence_before();
@@ -991,10 +1043,10 @@ int dispatch_major_2cta(int a_mn, int b_mn, const CUtensorMap& ma, const CUtenso
   return launch_2cta<BN, true, false>(ma, mb, p, s);
 }
 
-template <int BN, bool A_MN, bool B_MN>
+template <int BN, bool A_MN, bool B_MN, bool RS>
 int launch_persist(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p, cudaStream_t s) {
-  using C = CfgP<BN, B_MN>;
-  auto kern = gemm_bf16_tcgen05_persist_kernel<BN, A_MN, B_MN>;
+  using C = CfgP<BN, B_MN, RS>;
+  auto kern = gemm_bf16_tcgen05_persist_kernel<BN, A_MN, B_MN, RS>;
   static bool attr_done[64] = {false};
   static int sms[64] = {0};
   int dev = 0;
@@ -1018,10 +1070,14 @@ int launch_persist(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParam
 template <int BN>
 int dispatch_major_persist(int a_mn, int b_mn, const CUtensorMap& ma, const CUtensorMap& mb,
                            const GemmParams& p, cudaStream_t s) {
-  if (!a_mn && !b_mn) return launch_persist<BN, false, false>(ma, mb, p, s);
-  if (!a_mn && b_mn) return launch_persist<BN, false, true>(ma, mb, p, s);
-  if (a_mn && b_mn) return launch_persist<BN, true, true>(ma, mb, p, s);
-  return launch_persist<BN, true, false>(ma, mb, p, s);
+  if (p.rs_on) {   // wgrad is the only product with the reduce-scatter epilogue
+    if (a_mn && b_mn) return launch_persist<BN, true, true, true>(ma, mb, p, s);
+    B200_REQUIRE(false, "gemm: the persistent reduce-scatter epilogue is built for MN-major operands only");
+  }
+  if (!a_mn && !b_mn) return launch_persist<BN, false, false, false>(ma, mb, p, s);
+  if (!a_mn && b_mn) return launch_persist<BN, false, true, false>(ma, mb, p, s);
+  if (a_mn && b_mn) return launch_persist<BN, true, true, false>(ma, mb, p, s);
+  return launch_persist<BN, true, false, false>(ma, mb, p, s);
 }
 
 // Kernel choice. kind 0: one 128 x BN tile per CTA; 1: one 256 x BN tile per CTA pair;
@@ -1031,7 +1087,7 @@ int dispatch_major_persist(int a_mn, int b_mn, const CUtensorMap& ma, const CUte
 struct Plan { int kind, bn; };
 int g_force_kind = -2, g_force_bn = 0;
 
-Plan choose(int M, int N, bool rs_on) {
+Plan choose(int M, int N, bool rs_on, bool both_mn) {
   if (g_force_kind == -2) {
     g_force_kind = -1;
     if (const char* e = getenv("B200DP_GEMM_VARIANT")) {
@@ -1040,9 +1096,12 @@ Plan choose(int M, int N, bool rs_on) {
     }
   }
   const int small_bn = (N <= 16) ? 16 : (N <= 32 ? 32 : (N <= 64 ? 64 : 128));
-  const bool pair_ok = !rs_on && N >= 128 && M > 128;
+  // the reduce-scatter epilogue exists in the one-CTA kernel and, for wgrad's MN-major
+  // operands, in the persistent kernel
+  const bool persist_ok = N >= 128 && M > 128 && (!rs_on || both_mn);
+  const bool pair_ok = persist_ok && !rs_on;
   if (g_force_kind >= 0) {
-    if (g_force_kind >= 1 && pair_ok) {
+    if ((g_force_kind == 1 && pair_ok) || (g_force_kind >= 2 && persist_ok)) {
       int bn = g_force_bn ? g_force_bn : (N >= 256 ? 256 : 128);
       if (bn != 128 && bn != 256) bn = 256;
       if (N < bn) bn = 128;
@@ -1054,8 +1113,8 @@ Plan choose(int M, int N, bool rs_on) {
     if (bn > small_bn && bn != 256) bn = small_bn;
     return {0, bn};
   }
-  // automatic
-  if (pair_ok) {
+  // automatic (thresholds from scripts/gemm_experiment.py on B200)
+  if (persist_ok) {
     const long long t256 = (long long)((M + 255) / 256) * ((N + 255) / 256);
     if (N >= 256 && t256 >= 56) return {2, 256};
     const long long t128 = (long long)((M + 255) / 256) * ((N + 127) / 128);
@@ -1117,7 +1176,7 @@ int b200_gemm_bf16_rs(const void* A, int a_mn, long long lda, const void* B, int
                       size_t rs_slice_vec, size_t rs_base_vec, const unsigned* rs_seq,
                       void* stream) {
   B200_REQUIRE(M > 0 && N > 0 && K > 0, "b200_gemm_bf16: empty problem");
-  const Plan plan = choose(M, N, rs_comm != nullptr);
+  const Plan plan = choose(M, N, rs_comm != nullptr, a_mn && b_mn);
   const int BN = plan.bn;
   const int bn2 = plan.kind ? plan.bn : 0;      // CTA-pair kernels: each CTA loads half of the B tile
   CUtensorMap ma, mb;

@@ -227,6 +227,36 @@ def mlp_ddp(rank, world, backend, out_dir, algo):
     P.destroy_process_group()
 
 
+def gemm_rs(rank, world, backend, out_dir, kind, bn):
+    """Fused GEMM -> reduce-scatter: the wgrad tile vectors go straight into the owner ranks'
+    two-shot staging over peer memory; the bucket kernel then skips its own scatter phase."""
+    import importlib
+    P = _pg()
+    gemm = importlib.import_module(PKG + ".ops.gemm")
+    comm = P.init_process_group(backend=backend, rank=rank, world_size=world)
+    dev = comm.device
+    M, N, K = 1024, 784, 520           # 784 = 3 x 256 + 16: a ragged last tile column
+    g = torch.Generator().manual_seed(7 + rank)
+    dy = torch.randn(K, M, generator=g).to(torch.bfloat16).to(dev)
+    x = torch.randn(K, N, generator=g).to(torch.bfloat16).to(dev)
+    bucket = torch.zeros(M * N, dtype=torch.bfloat16, device=dev)
+    tgt = dict(comm.rs_target(bucket.numel() * 2, channel=3))
+    tgt["base_vec"] = 0
+    gemm.set_variant(kind, bn)
+    for _ in range(3):                 # the staging slots alternate between rounds
+        bucket.zero_()
+        gemm.gemm_bf16(dy, x, True, True, out=bucket.view(M, N), rs=tgt)
+        comm.all_reduce(bucket, op="mean", algo="twoshot", channel=3,
+                        push_from=bucket.numel() * 2 // 16)
+    gemm.set_variant("auto")
+    torch.cuda.synchronize()
+    comm.check_errors()
+    torch.save({"got": bucket.float().cpu().view(M, N),
+                "local": (dy.float().t() @ x.float()).cpu()},
+               os.path.join(out_dir, f"rs_{rank}.pt"))
+    P.destroy_process_group()
+
+
 def trainer_dist(rank, world, backend, out_dir):
     """The reference's train_dist.py script body on `world` ranks (src/train_dist.py:118-164)."""
     import importlib

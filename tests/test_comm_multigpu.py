@@ -96,6 +96,18 @@ def test_mlp_ddp_peer(native_lib, tmp_path, algo):
         assert err < 0.3, f"update mismatch {err:.3f} for {s.name}"
 
 
+@pytest.mark.parametrize("kind,bn", [("cta", 128), ("persistent", 256), ("persistent", 128)])
+def test_gemm_reduce_scatter_peer(native_lib, tmp_path, kind, bn):
+    """GEMM with the reduce-scatter epilogue + the bucket kernel == mean of the per-rank products."""
+    world = _world()
+    launch(_workers.gemm_rs, world, args=("b200", str(tmp_path), kind, bn), timeout=600)
+    res = [torch.load(tmp_path / f"rs_{r}.pt") for r in range(world)]
+    want = sum(r["local"].to(torch.bfloat16).float() for r in res) / world
+    for r in range(world):
+        assert torch.equal(res[r]["got"], res[0]["got"])
+        torch.testing.assert_close(res[r]["got"], want, rtol=1.6e-2, atol=0.3)
+
+
 def test_trainer_distributed_peer(native_lib, tmp_path):
     world = 2 if torch.cuda.device_count() >= 2 else 0
     if not world:
