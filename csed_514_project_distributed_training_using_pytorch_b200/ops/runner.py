@@ -82,6 +82,13 @@ class NativeRunner:
                                         N.ptr(hloss), N.stream()), "b200_runner_run")
         self.engine.launches += steps * self.kernels_per_step
 
+    def chunks_launched(self) -> int:
+        """How many 16-step graphs (copies as graph nodes) have been launched; the remaining
+        steps went through the per-step submission path."""
+        f = N.lib().b200_runner_chunks_launched
+        f.restype, f.argtypes = C.c_longlong, [c_p]
+        return int(f(self._h)) if self._h else 0
+
     def close(self):
         if self._h:
             N.lib().b200_runner_destroy(self._h)

@@ -188,6 +188,7 @@ int b200_runner_config_size(void);
 int b200_runner_create(const void* cfg_blob, void** out);
 int b200_runner_run(void* h, const void* hx, const long long* hy, int steps, float* hloss,
                     void* caller_stream);
+long long b200_runner_chunks_launched(void* runner);   /* 16-step graphs launched so far */
 int b200_runner_destroy(void* h);
 int b200_pdl_enabled(void);
 int b200_net_set_phase_debug(long long* buf);

@@ -232,10 +232,11 @@ def test_sgd_kernel_matches_torch(cuda_device):
 
 
 def test_native_runner_matches_python_loop(cuda_device):
-    """csrc/runner.cu (3 staging slots, copy/compute overlap) == the Python step loop."""
+    """csrc/runner.cu (staging slots, copy/compute overlap, 16-step chunk graphs with the
+    copies as graph nodes, per-step submission for the remainder) == the Python step loop."""
     from csed_514_project_distributed_training_using_pytorch_b200.trainer import Trainer
     from csed_514_project_distributed_training_using_pytorch_b200.utils.config import TrainConfig
-    B, steps = 64, 20
+    B, steps = 64, 60
     g = torch.Generator().manual_seed(0)
     hx = torch.randn(steps * B, 784, generator=g).pin_memory()
     hy = torch.randint(0, 10, (steps * B,), generator=g).pin_memory()
@@ -243,10 +244,14 @@ def test_native_runner_matches_python_loop(cuda_device):
     for native in (True, False):
         tr = Trainer(TrainConfig(learning_rate=0.02), distributed_style=True)
         tr.native_runner = native
-        l1 = tr.train_steps_from_host(hx, hy, 12, B)
-        l2 = tr.train_steps_from_host(hx[12 * B:], hy[12 * B:], 8, B)   # second call: slots wrap
+        l1 = tr.train_steps_from_host(hx, hy, 12, B)                     # per-step path only
+        l2 = tr.train_steps_from_host(hx[12 * B:], hy[12 * B:], 41, B)   # 2 chunks + 9 single steps
+        l3 = tr.train_steps_from_host(hx[53 * B:], hy[53 * B:], 7, B)    # slots wrap after chunks
         torch.cuda.synchronize()
-        out.append((tr.engine.flat.param.clone(), torch.cat([l1, l2]).clone(), tr.engine.steps_done()))
+        if native:
+            assert tr._graphs[("runner", B, hx.dtype)].chunks_launched() == 2
+        out.append((tr.engine.flat.param.clone(), torch.cat([l1, l2, l3]).clone(),
+                    tr.engine.steps_done()))
     assert out[0][2] == out[1][2] == steps
     assert torch.equal(out[0][0], out[1][0])
     assert torch.equal(out[0][1], out[1][1])
