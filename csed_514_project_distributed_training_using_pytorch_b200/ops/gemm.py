@@ -10,6 +10,7 @@ from typing import Optional
 import torch
 
 from .. import _native as N
+N_ = N   # `N` is also the conventional name of a GEMM dimension below
 
 c_p, c_i, c_ll = C.c_void_p, C.c_int, C.c_longlong
 c_sz = C.c_size_t
@@ -19,9 +20,18 @@ N.register_sigs({
     "b200_gemm_bf16_rs": [c_p, c_i, c_ll, c_p, c_i, c_ll, c_p, c_i, c_ll, c_i, c_i, c_i, c_p, c_i,
                           c_p, c_ll, c_p, c_sz, c_sz, c_sz, c_sz, c_p, c_p],
     "b200_gemm_set_variant": [c_i, c_i],
+    "b200_gemm_plan": [c_i, c_i, c_i, c_i, C.POINTER(c_i), C.POINTER(c_i)],
 })
 
 VARIANTS = {"auto": -1, "cta": 0, "pair": 1, "persistent": 2}
+
+
+def plan(M: int, N: int, rs: bool = False, both_mn: bool = False):
+    """(kind, bn) the library would pick for an M x N output: kind "cta" | "pair" |
+    "persistent". Host-only (works without a GPU)."""
+    k, b = c_i(), c_i()
+    N_.call("b200_gemm_plan", M, N, int(rs), int(both_mn), C.byref(k), C.byref(b))
+    return {v: n for n, v in VARIANTS.items()}[k.value], b.value
 
 
 def set_variant(kind="auto", bn: int = 0):

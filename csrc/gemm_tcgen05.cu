@@ -11,15 +11,19 @@
 // so no operand is ever transposed in memory: the majorness goes into the TMA box shape,
 // the shared-memory matrix descriptor and two bits of the instruction descriptor.
 //
-// Structure (one 128 x BN output tile per CTA, 192 threads):
+// Roles (192 threads per CTA, in all three kernels):
 //   warp 0      TMA producer: cp.async.bulk.tensor.2d into a STAGES-deep ring of
 //               128B-swizzled A/B tiles, completion on `full` mbarriers (expect_tx)
-//   warp 1      TMEM allocator + MMA issuer: one elected lane issues
-//               tcgen05.mma.cta_group::1.kind::f16 (M=128, N=BN, K=16) four times per
-//               64-wide K block; tcgen05.commit releases the smem stage (`empty`) and
-//               finally signals `tmem_full`
+//   warp 1      TMEM allocator + MMA issuer: one elected lane issues tcgen05.mma.kind::f16
+//               (K=16) four times per 64-wide K block; tcgen05.commit releases the smem
+//               stage (`empty`) and finally signals `tmem_full`
 //   warps 2..5  epilogue: tcgen05.ld 32x32b.x32 (each warp its own 32 TMEM lanes = 32 rows),
 //               bias / ReLU / ReLU-mask, bf16 or fp32 stores with edge masking
+// Kernels (host-side choose() picks by shape):
+//   gemm_bf16_tcgen05_kernel          one 128 x BN tile per CTA (BN 16..256), cta_group::1
+//   gemm_bf16_tcgen05_2cta_kernel     one 256 x BN tile per CTA pair, cta_group::2
+//   gemm_bf16_tcgen05_persist_kernel  CTA pairs looping over tiles, two TMEM accumulators so
+//                                     the epilogue of tile i overlaps the main loop of i+1
 // TMA zero-fills out-of-bounds reads, so M, N, K need no padding (only 16-byte row pitch).
 #include <cuda.h>
 #include <cuda_bf16.h>
@@ -1150,6 +1154,14 @@ int b200_gemm_bf16_rs(const void* A, int a_mn, long long lda, const void* B, int
                       const void* rs_comm, size_t rs_stage_off, size_t rs_src_bytes,
                       size_t rs_slice_vec, size_t rs_base_vec, const unsigned* rs_seq,
                       void* stream);
+
+// Which kernel a problem would get (host-only, no GPU needed): kind 0 / 1 / 2 and the tile width.
+int b200_gemm_plan(int M, int N, int rs_on, int both_mn, int* kind, int* bn) {
+  const Plan p = choose(M, N, rs_on != 0, both_mn != 0);
+  if (kind) *kind = p.kind;
+  if (bn) *bn = p.bn;
+  return 0;
+}
 
 // Pin the kernel kind / tile width (see choose()); kind = -1 restores the automatic choice.
 int b200_gemm_set_variant(int kind, int bn) {

@@ -42,3 +42,30 @@ def test_reducer_core_ready_counting(native_lib):
     assert core.all_done() and core.completion_order() == [0, 1]
     core.reset()
     assert core.pending_buckets() == [0, 1] and core.completion_order() == []
+
+
+def test_gemm_kernel_plan_host_only(native_lib):
+    """Shape -> kernel choice of the tcgen05 GEMM (csrc/gemm_tcgen05.cu choose()); host-only."""
+    from csed_514_project_distributed_training_using_pytorch_b200.ops import gemm
+    try:
+        # the wide-MLP products at per-GPU batch 512 (BASELINE.json config 4)
+        assert gemm.plan(4096, 4096) == ("persistent", 256)             # fc2 wgrad
+        assert gemm.plan(4096, 4096, rs=True, both_mn=True) == ("persistent", 256)
+        assert gemm.plan(4096, 784, rs=True, both_mn=True) == ("persistent", 256)   # fc1 wgrad
+        assert gemm.plan(512, 4096) == ("persistent", 128)              # fc2 forward / dgrad
+        # the reduce-scatter epilogue of other layouts stays on the one-CTA kernel
+        assert gemm.plan(4096, 4096, rs=True, both_mn=False) == ("cta", 128)
+        # skinny problems: one CTA per tile, tile width follows N
+        assert gemm.plan(64, 4096) == ("cta", 128)
+        assert gemm.plan(4096, 10) == ("cta", 16)
+        assert gemm.plan(512, 40) == ("cta", 64)
+        # pinning
+        gemm.set_variant("pair", 128)
+        assert gemm.plan(4096, 4096) == ("pair", 128)
+        assert gemm.plan(64, 4096)[0] == "cta"                          # pairs need M > 128
+        gemm.set_variant("cta", 256)
+        assert gemm.plan(4096, 4096) == ("cta", 256)
+        assert gemm.plan(100, 100) == ("cta", 128)
+    finally:
+        gemm.set_variant("auto")
+    assert gemm.plan(4096, 4096) == ("persistent", 256)
