@@ -404,7 +404,7 @@ __device__ __forceinline__ void epilogue_direct(const GemmParams& p, uint32_t tm
     for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
     const bool full_chunk = col0 + 32 <= p.N;
     if (p.bias) {
-      if (full_chunk) {
+      if (full_chunk && (reinterpret_cast<uintptr_t>(p.bias) & 15) == 0) {
 #pragma unroll
         for (int j = 0; j < 32; j += 8) {
           const uint4 bv = *reinterpret_cast<const uint4*>(p.bias + col0 + j);

@@ -99,3 +99,19 @@ def test_gemm_many_tiles_per_cluster(cuda_device, restore_variant, kind, bn):
     dW = gemm.linear_wgrad(dy[:, :512].contiguous(), dy[:, 512:1024].contiguous())
     want_dW = dy[:, :512].float().t() @ dy[:, 512:1024].float()
     torch.testing.assert_close(dW.float(), want_dW, rtol=1.6e-2, atol=0.6)
+
+
+@pytest.mark.parametrize("kind,bn", [("cta", 128), ("persistent", 256)])
+def test_gemm_bias_view_with_odd_offset(cuda_device, restore_variant, kind, bn):
+    """A bias that is a view at a 2-byte offset (not 16-byte aligned) takes the scalar path."""
+    g = torch.Generator().manual_seed(3)
+    M, N, K = 512, 512, 128
+    x = torch.randn(M, K, generator=g).to(torch.bfloat16).to(cuda_device)
+    W = (torch.randn(N, K, generator=g) / 8).to(torch.bfloat16).to(cuda_device)
+    bbuf = torch.randn(N + 8, generator=g).to(torch.bfloat16).to(cuda_device)
+    b = bbuf[1:N + 1]
+    assert b.data_ptr() % 16 != 0
+    gemm.set_variant(kind, bn)
+    y = gemm.linear_fwd(x, W, b, relu=True)
+    want = torch.relu(x.float() @ W.float().t() + b.float())
+    torch.testing.assert_close(y.float(), want, rtol=1.6e-2, atol=3e-2)
