@@ -396,7 +396,7 @@ class Trainer:
         if loss_out is None:
             loss_out = torch.empty(steps, dtype=torch.float32).pin_memory()
         if self.cfg.cuda_graph and self.native_runner:
-            # native loop (csrc/runner.cu): 3 staging slots, copy/compute overlap, no Python
+            # native loop (csrc/runner.cu): per-step copies, 16-step kernel graphs, no Python
             key = ("runner", batch, hx.dtype)
             r = self._graphs.get(key)
             if r is None:
