@@ -20,24 +20,27 @@ N.register_sigs({
     "b200_gemm_bf16_rs": [c_p, c_i, c_ll, c_p, c_i, c_ll, c_p, c_i, c_ll, c_i, c_i, c_i, c_p, c_i,
                           c_p, c_ll, c_p, c_sz, c_sz, c_sz, c_sz, c_p, c_p],
     "b200_gemm_set_variant": [c_i, c_i],
-    "b200_gemm_plan": [c_i, c_i, c_i, c_i, C.POINTER(c_i), C.POINTER(c_i)],
+    "b200_gemm_plan": [c_i, c_i, c_i, c_i, c_i, C.POINTER(c_i), C.POINTER(c_i), C.POINTER(c_i)],
 })
 
-VARIANTS = {"auto": -1, "cta": 0, "pair": 1, "persistent": 2}
+VARIANTS = {"auto": -1, "cta": 0, "pair": 1, "persistent": 2, "splitk": 3}
 
 
-def plan(M: int, N: int, rs: bool = False, both_mn: bool = False):
-    """(kind, bn) the library would pick for an M x N output: kind "cta" | "pair" |
-    "persistent". Host-only (works without a GPU)."""
-    k, b = c_i(), c_i()
-    N_.call("b200_gemm_plan", M, N, int(rs), int(both_mn), C.byref(k), C.byref(b))
-    return {v: n for n, v in VARIANTS.items()}[k.value], b.value
+def plan(M: int, N: int, K: int = 4096, rs: bool = False, both_mn: bool = False):
+    """(kind, bn) the library would pick for an M x N x K product: kind "cta" | "pair" |
+    "persistent" | "splitk" (persistent with every tile split in two along K). Host-only
+    (works without a GPU)."""
+    k, b, sp = c_i(), c_i(), c_i()
+    N_.call("b200_gemm_plan", M, N, K, int(rs), int(both_mn), C.byref(k), C.byref(b), C.byref(sp))
+    name = {v: n for n, v in VARIANTS.items()}[k.value]
+    return ("splitk" if sp.value == 2 else name), b.value
 
 
 def set_variant(kind="auto", bn: int = 0):
     """Pin the GEMM kernel for tests / benchmarks: "cta" (one 128 x bn tile per CTA), "pair"
     (one 256 x bn tile per CTA pair, cta_group::2), "persistent" (CTA pairs looping over
-    tiles with double-buffered TMEM) or "auto" (shape-based choice, the default)."""
+    tiles with double-buffered TMEM), "splitk" (persistent, each tile as two K halves on two
+    CTA pairs) or "auto" (shape-based choice, the default)."""
     N.call("b200_gemm_set_variant", VARIANTS[kind] if isinstance(kind, str) else int(kind), int(bn))
 
 

@@ -226,6 +226,13 @@ struct GemmParams {
   size_t rs_sl;          // vectors per owner slice
   size_t rs_base_vec;    // vector index of C[0][0] inside the bucket
   const unsigned* rs_seq;  // the bucket channel's sequence counter (slot = (seq+1) & 1)
+  // Split-K (persistent kernel only): with ksplit = 2 every output tile is two work units.
+  // The unit with the upper half of K stores its raw fp32 accumulators into sk_ws
+  // [tile][256][BN] and raises sk_flags[tile]; the unit with the lower half adds them in its
+  // epilogue. The flags count 8 producer warps + 8 consumer warps and reset themselves.
+  int ksplit;
+  float* sk_ws;
+  unsigned* sk_flags;
 };
 
 template <int BN, bool B_MN> struct Cfg {
@@ -384,9 +391,11 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint8_t* tile
 // applies bias / ReLU / mask and stores 64-byte (bf16) or 128-byte (fp32) row pieces directly.
 // `release` is called once, as soon as the last TMEM read of the tile has landed in registers,
 // so the MMA warp can start the tile after next in this accumulator buffer.
+// `partial`: this lane's row of a split-K partner's fp32 accumulators (BN floats), or null.
 template <int BN, typename Release>
 __device__ __forceinline__ void epilogue_direct(const GemmParams& p, uint32_t tmem_acc, int warp,
-                                                int lane, int m0, int n0, Release release) {
+                                                int lane, int m0, int n0, const float* partial,
+                                                Release release) {
   const int lg = warp & 3;
   const int row = m0 + lg * 32 + lane;
   const bool row_ok = row < p.M;
@@ -402,6 +411,13 @@ __device__ __forceinline__ void epilogue_direct(const GemmParams& p, uint32_t tm
     float v[32];
 #pragma unroll
     for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+    if (partial) {
+#pragma unroll
+      for (int j = 0; j < 32; j += 4) {
+        const float4 q = __ldcg(reinterpret_cast<const float4*>(partial + c0 + j));
+        v[j] += q.x; v[j + 1] += q.y; v[j + 2] += q.z; v[j + 3] += q.w;
+      }
+    }
     const bool full_chunk = col0 + 32 <= p.N;
     if (p.bias) {
       if (full_chunk && (reinterpret_cast<uintptr_t>(p.bias) & 15) == 0) {
@@ -475,6 +491,25 @@ __device__ __forceinline__ void epilogue_direct(const GemmParams& p, uint32_t tm
           if (col0 + j < p.N) crow[j] = __float2bfloat16_rn(v[j]);
       }
     }
+  }
+}
+
+// Split-K producer epilogue: raw fp32 accumulators of this lane's row -> workspace.
+template <int BN, typename Release>
+__device__ __forceinline__ void epilogue_store_partial(uint32_t tmem_acc, int warp, int lane,
+                                                       float* dst_row, Release release) {
+  const int lg = warp & 3;
+#pragma unroll 1
+  for (int c0 = 0; c0 < BN; c0 += 32) {
+    uint32_t r[32];
+    tmem_ld32(tmem_acc + ((uint32_t)(lg * 32) << 16) + (uint32_t)c0, r);
+    tmem_ld_wait();
+    if (c0 + 32 >= BN) release();
+#pragma unroll
+    for (int j = 0; j < 32; j += 4)
+      __stcg(reinterpret_cast<float4*>(dst_row + c0 + j),
+             make_float4(__uint_as_float(r[j]), __uint_as_float(r[j + 1]),
+                         __uint_as_float(r[j + 2]), __uint_as_float(r[j + 3])));
   }
 }
 
@@ -849,6 +884,13 @@ gemm_bf16_tcgen05_persist_kernel(const __grid_constant__ CUtensorMap map_a,
   const int tiles_m = (p.M + 255) / 256;
   const int num_tiles = tiles_m * ((p.N + BN - 1) / BN);
   const int num_kb = (p.K + BK - 1) / BK;
+  // Work units. Without split-K a unit is a tile. With ksplit = 2, units [0, num_tiles) are
+  // the PRODUCER halves (upper half of K) and [num_tiles, 2 num_tiles) the consumer halves of
+  // the same tiles: every cluster walks its units in ascending order, so whatever a consumer
+  // waits for is queued ahead of every consumer on its own cluster, and producers never wait.
+  const int ksplit = RS ? 1 : p.ksplit;
+  const int num_units = num_tiles * ksplit;
+  const int kb_half = (num_kb + ksplit - 1) / ksplit;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&map_a);
@@ -875,10 +917,14 @@ gemm_bf16_tcgen05_persist_kernel(const __grid_constant__ CUtensorMap map_a,
     // ===== TMA producer (both CTAs): the ring keeps rolling across tiles =====
     if (lane == 0) {
       uint32_t it = 0;
-      for (int t = cluster_id; t < num_tiles; t += num_clusters) {
+      for (int u = cluster_id; u < num_units; u += num_clusters) {
+        const int t = u % num_tiles;
+        const bool upper = ksplit == 2 && u < num_tiles;
+        const int kb_begin = upper ? kb_half : 0;
+        const int kb_end = (ksplit == 2 && !upper) ? kb_half : num_kb;
         const int m0 = (t % tiles_m) * 256 + (int)rank * BM;
         const int nb0 = (t / tiles_m) * BN + (int)rank * (BN / 2);
-        for (int kb = 0; kb < num_kb; ++kb, ++it) {
+        for (int kb = kb_begin; kb < kb_end; ++kb, ++it) {
           const uint32_t s = it % C::STAGES;
           const uint32_t ph = (it / C::STAGES) & 1;
           mbar_wait_role(&empty[s], ph ^ 1);
@@ -908,12 +954,15 @@ gemm_bf16_tcgen05_persist_kernel(const __grid_constant__ CUtensorMap map_a,
     if (rank == 0 && lane == 0) {
       constexpr uint32_t idesc = make_idesc(256, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
       uint32_t it = 0, tcount = 0;
-      for (int t = cluster_id; t < num_tiles; t += num_clusters, ++tcount) {
+      for (int u = cluster_id; u < num_units; u += num_clusters, ++tcount) {
+        const bool upper = ksplit == 2 && u < num_tiles;
+        const int kb_begin = upper ? kb_half : 0;
+        const int kb_end = (ksplit == 2 && !upper) ? kb_half : num_kb;
         const uint32_t buf = tcount & 1, use = tcount >> 1;
         mbar_wait_role(&tmem_empty[buf], (use & 1) ^ 1);    // both CTAs drained this buffer
         tcgen05_fence_after();
         const uint32_t acc = tmem_base + buf * BN;
-        for (int kb = 0; kb < num_kb; ++kb, ++it) {
+        for (int kb = kb_begin; kb < kb_end; ++kb, ++it) {
           const uint32_t s = it % C::STAGES;
           const uint32_t ph = (it / C::STAGES) & 1;
           mbar_wait_role(&full[s], ph);
@@ -926,7 +975,7 @@ gemm_bf16_tcgen05_persist_kernel(const __grid_constant__ CUtensorMap map_a,
                                         : make_smem_desc(a_addr + k * UMMA_K * 2, 16, 1024);
             const uint64_t bdesc = B_MN ? make_smem_desc(b_addr + k * UMMA_K * 128, BK * 128, 1024)
                                         : make_smem_desc(b_addr + k * UMMA_K * 2, 16, 1024);
-            umma_bf16_2sm(acc, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+            umma_bf16_2sm(acc, adesc, bdesc, idesc, (kb != kb_begin || k != 0) ? 1u : 0u);
           }
           umma_commit_2sm(&empty[s]);        // frees the stage in BOTH CTAs
         }
@@ -937,7 +986,8 @@ gemm_bf16_tcgen05_persist_kernel(const __grid_constant__ CUtensorMap map_a,
     // ===== epilogue warps (both CTAs) =====
     const uint32_t lead_empty0 = mapa_shared(smem_u32(&tmem_empty[0]), 0);
     uint32_t tcount = 0;
-    for (int t = cluster_id; t < num_tiles; t += num_clusters, ++tcount) {
+    for (int u = cluster_id; u < num_units; u += num_clusters, ++tcount) {
+      const int t = u % num_tiles;
       const uint32_t buf = tcount & 1, use = tcount >> 1;
       const int m0 = (t % tiles_m) * 256 + (int)rank * BM;
       const int n0 = (t / tiles_m) * BN;
@@ -948,10 +998,33 @@ gemm_bf16_tcgen05_persist_kernel(const __grid_constant__ CUtensorMap map_a,
         __syncwarp();
         if (lane == 0) mbar_arrive_cluster(lead_empty0 + buf * 8);
       };
-      if constexpr (RS)
+      if constexpr (RS) {
         epilogue_rs_staged<BN>(p, epi_stage, tmem_base + buf * BN, warp, lane, m0, n0, release);
-      else
-        epilogue_direct<BN>(p, tmem_base + buf * BN, warp, lane, m0, n0, release);
+      } else if (ksplit == 2) {
+        // this lane's row of the tile's fp32 partial: [tile][256 rows][BN]
+        float* prow = p.sk_ws + ((size_t)t * 256 + rank * BM + (warp & 3) * 32 + lane) * BN;
+        unsigned* flag = p.sk_flags + t;
+        if (u < num_tiles) {
+          epilogue_store_partial<BN>(tmem_base + buf * BN, warp, lane, prow, release);
+          __threadfence();
+          __syncwarp();
+          if (lane == 0) red_release_gpu_add_u32(flag, 1u);
+        } else {
+          if (lane == 0) {        // all 8 producer warps of the tile have published their rows
+            uint32_t n = 0;
+            while (ld_acquire_gpu_u32(flag) < 8u) {
+              __nanosleep(64);
+              if (++n > (1u << 25)) __trap();
+            }
+          }
+          __syncwarp();
+          epilogue_direct<BN>(p, tmem_base + buf * BN, warp, lane, m0, n0, prow, release);
+          __syncwarp();
+          if (lane == 0 && atomicAdd(flag, 1u) == 15u) atomicExch(flag, 0u);   // last reader resets
+        }
+      } else {
+        epilogue_direct<BN>(p, tmem_base + buf * BN, warp, lane, m0, n0, nullptr, release);
+      }
     }
   }
   tcgen05_fence_before();
@@ -1060,7 +1133,7 @@ int launch_persist(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParam
     B200_CUDA_OK(cudaDeviceGetAttribute(&sms[dev & 63], cudaDevAttrMultiProcessorCount, dev));
     attr_done[dev & 63] = true;
   }
-  const int tiles = ((p.M + 255) / 256) * ((p.N + BN - 1) / BN);
+  const int tiles = ((p.M + 255) / 256) * ((p.N + BN - 1) / BN) * (RS ? 1 : p.ksplit);   // work units
   int clusters = sms[dev & 63] / 2;                 // one CTA pair per TPC
   if (clusters > tiles) clusters = tiles;
   // same makespan with fewer pairs when the last wave would be ragged (less L2 contention)
@@ -1085,13 +1158,14 @@ int dispatch_major_persist(int a_mn, int b_mn, const CUtensorMap& ma, const CUte
 }
 
 // Kernel choice. kind 0: one 128 x BN tile per CTA; 1: one 256 x BN tile per CTA pair;
-// 2: persistent CTA pairs with double-buffered TMEM. b200_gemm_set_variant (or
-// B200DP_GEMM_VARIANT=kind[,bn]) pins the kind (and optionally BN) for tests and benchmarks;
-// -1 = automatic.
-struct Plan { int kind, bn; };
+// 2: persistent CTA pairs with double-buffered TMEM; 3 (forcing only): kind 2 with split-K.
+// b200_gemm_set_variant (or B200DP_GEMM_VARIANT=kind[,bn]) pins the kind (and optionally BN)
+// for tests and benchmarks; -1 = automatic.
+struct Plan { int kind, bn, ksplit; };
 int g_force_kind = -2, g_force_bn = 0;
+constexpr int SK_MAX_TILES = 37;     // 2 x 37 work units fill the 74 CTA pairs in one wave
 
-Plan choose(int M, int N, bool rs_on, bool both_mn) {
+Plan choose(int M, int N, int K, bool rs_on, bool both_mn, bool allow_split) {
   if (g_force_kind == -2) {
     g_force_kind = -1;
     if (const char* e = getenv("B200DP_GEMM_VARIANT")) {
@@ -1104,28 +1178,95 @@ Plan choose(int M, int N, bool rs_on, bool both_mn) {
   // operands, in the persistent kernel
   const bool persist_ok = N >= 128 && M > 128 && (!rs_on || both_mn);
   const bool pair_ok = persist_ok && !rs_on;
+  const long long t256 = (long long)((M + 255) / 256) * ((N + 255) / 256);
+  const int num_kb = (K + BK - 1) / BK;
+  const bool split_ok = allow_split && pair_ok && N >= 256 && t256 <= SK_MAX_TILES && num_kb >= 2;
   if (g_force_kind >= 0) {
+    if (g_force_kind == 3 && split_ok) return {2, 256, 2};
     if ((g_force_kind == 1 && pair_ok) || (g_force_kind >= 2 && persist_ok)) {
       int bn = g_force_bn ? g_force_bn : (N >= 256 ? 256 : 128);
       if (bn != 128 && bn != 256) bn = 256;
       if (N < bn) bn = 128;
-      return {g_force_kind > 2 ? 2 : g_force_kind, bn};
+      return {g_force_kind >= 2 ? 2 : 1, bn, 1};
     }
     int bn = g_force_bn ? g_force_bn : small_bn;
     if (bn == 256 && (N < 256 || rs_on)) bn = small_bn;
     if (bn != 16 && bn != 32 && bn != 64 && bn != 128 && bn != 256) bn = small_bn;
     if (bn > small_bn && bn != 256) bn = small_bn;
-    return {0, bn};
+    return {0, bn, 1};
   }
   // automatic (thresholds from scripts/gemm_experiment.py on B200)
   if (persist_ok) {
-    const long long t256 = (long long)((M + 255) / 256) * ((N + 255) / 256);
-    if (N >= 256 && t256 >= 56) return {2, 256};
+    if (N >= 256 && t256 >= 56) return {2, 256, 1};
+    // Split-K (kind 3) is NOT chosen automatically: at 512 x 4096 x 4096 (32 tiles, 64 K
+    // blocks) it measured 0.39 PFLOP/s against 0.53 for 256 x 128 tiles, because the serial
+    // tail (producer epilogue -> flag -> consumer epilogue reading the partial tile from L2)
+    // costs more than the halved main loop saves.
     const long long t128 = (long long)((M + 255) / 256) * ((N + 127) / 128);
-    if (t128 >= 56) return {2, 128};
+    if (t128 >= 56) return {2, 128, 1};
   }
-  if (!rs_on && N >= 256 && (long long)((M + 127) / 128) * ((N + 255) / 256) >= 120) return {0, 256};
-  return {0, small_bn};
+  if (!rs_on && N >= 256 && (long long)((M + 127) / 128) * ((N + 255) / 256) >= 120) return {0, 256, 1};
+  return {0, small_bn, 1};
+}
+
+// Split-K workspaces: a small per-device pool (fp32 partial tiles + self-resetting flags),
+// one slot per stream that uses split-K, allocated on the first use OUTSIDE stream capture.
+// While it does not exist (or every slot is taken) the caller falls back to the unsplit plan,
+// so nothing is ever allocated during a capture.
+constexpr int SK_SLOTS = 4;
+struct SkPool {
+  float* ws[SK_SLOTS];
+  unsigned* flags[SK_SLOTS];
+  cudaStream_t owner[SK_SLOTS];
+  int used;
+  bool ready;
+};
+SkPool g_sk[64];
+std::mutex g_sk_mu;
+
+bool sk_acquire(cudaStream_t s, float** ws, unsigned** flags) {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return false;
+  std::lock_guard<std::mutex> lock(g_sk_mu);
+  SkPool& P = g_sk[dev & 63];
+  if (!P.ready) {
+    cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(s, &st) != cudaSuccess || st != cudaStreamCaptureStatusNone) {
+      cudaGetLastError();
+      return false;
+    }
+    const size_t ws_bytes = (size_t)SK_MAX_TILES * 256 * 256 * sizeof(float);
+    bool ok = true;
+    for (int i = 0; i < SK_SLOTS && ok; ++i) {
+      ok = cudaMalloc((void**)&P.ws[i], ws_bytes) == cudaSuccess &&
+           cudaMalloc((void**)&P.flags[i], 256) == cudaSuccess &&
+           cudaMemset(P.flags[i], 0, 256) == cudaSuccess;
+    }
+    ok = ok && cudaDeviceSynchronize() == cudaSuccess;
+    if (!ok) {   // e.g. another thread is capturing in global mode: try again at a later call
+      cudaGetLastError();
+      for (int i = 0; i < SK_SLOTS; ++i) {
+        if (P.ws[i]) cudaFree(P.ws[i]);
+        if (P.flags[i]) cudaFree(P.flags[i]);
+        P.ws[i] = nullptr;
+        P.flags[i] = nullptr;
+      }
+      cudaGetLastError();
+      return false;
+    }
+    P.ready = true;
+  }
+  int slot = -1;
+  for (int i = 0; i < P.used; ++i)
+    if (P.owner[i] == s) slot = i;
+  if (slot < 0) {
+    if (P.used == SK_SLOTS) return false;
+    slot = P.used++;
+    P.owner[slot] = s;
+  }
+  *ws = P.ws[slot];
+  *flags = P.flags[slot];
+  return true;
 }
 
 template <int BN>
@@ -1156,10 +1297,11 @@ int b200_gemm_bf16_rs(const void* A, int a_mn, long long lda, const void* B, int
                       void* stream);
 
 // Which kernel a problem would get (host-only, no GPU needed): kind 0 / 1 / 2 and the tile width.
-int b200_gemm_plan(int M, int N, int rs_on, int both_mn, int* kind, int* bn) {
-  const Plan p = choose(M, N, rs_on != 0, both_mn != 0);
+int b200_gemm_plan(int M, int N, int K, int rs_on, int both_mn, int* kind, int* bn, int* ksplit) {
+  const Plan p = choose(M, N, K, rs_on != 0, both_mn != 0, true);
   if (kind) *kind = p.kind;
   if (bn) *bn = p.bn;
+  if (ksplit) *ksplit = p.ksplit;
   return 0;
 }
 
@@ -1188,7 +1330,12 @@ int b200_gemm_bf16_rs(const void* A, int a_mn, long long lda, const void* B, int
                       size_t rs_slice_vec, size_t rs_base_vec, const unsigned* rs_seq,
                       void* stream) {
   B200_REQUIRE(M > 0 && N > 0 && K > 0, "b200_gemm_bf16: empty problem");
-  const Plan plan = choose(M, N, rs_comm != nullptr, a_mn && b_mn);
+  cudaStream_t s = (cudaStream_t)stream;
+  Plan plan = choose(M, N, K, rs_comm != nullptr, a_mn && b_mn, true);
+  float* sk_ws = nullptr;
+  unsigned* sk_flags = nullptr;
+  if (plan.ksplit == 2 && !sk_acquire(s, &sk_ws, &sk_flags))
+    plan = choose(M, N, K, rs_comm != nullptr, a_mn && b_mn, false);
   const int BN = plan.bn;
   const int bn2 = plan.kind ? plan.bn : 0;      // CTA-pair kernels: each CTA loads half of the B tile
   CUtensorMap ma, mb;
@@ -1206,6 +1353,9 @@ int b200_gemm_bf16_rs(const void* A, int a_mn, long long lda, const void* B, int
   p.relu = relu;
   p.relu_mask = (const __nv_bfloat16*)relu_mask;
   p.ld_mask = (int)ld_mask;
+  p.ksplit = plan.ksplit;
+  p.sk_ws = sk_ws;
+  p.sk_flags = sk_flags;
   p.rs_on = 0;
   if (rs_comm) {
     B200_REQUIRE(!c_fp32 && ldc == N && N % 8 == 0 && !bias && !relu && !relu_mask,
@@ -1218,7 +1368,6 @@ int b200_gemm_bf16_rs(const void* A, int a_mn, long long lda, const void* B, int
     p.rs_base_vec = rs_base_vec;
     p.rs_seq = rs_seq;
   }
-  cudaStream_t s = (cudaStream_t)stream;
   if (plan.kind == 2)
     return BN == 256 ? dispatch_major_persist<256>(a_mn, b_mn, ma, mb, p, s)
                      : dispatch_major_persist<128>(a_mn, b_mn, ma, mb, p, s);

@@ -170,11 +170,12 @@ int b200_gemm_bf16_rs(const void* A, int a_mn, long long lda, const void* B, int
                       size_t rs_slice_vec, size_t rs_base_vec, const unsigned* rs_seq,
                       void* stream);
 /* Pin the GEMM kernel: kind 0 = one 128 x bn tile per CTA (bn 16..256), 1 = one 256 x bn tile
- * per CTA pair (cta_group::2), 2 = persistent CTA pairs with double-buffered TMEM; bn 0 = pick.
+ * per CTA pair (cta_group::2), 2 = persistent CTA pairs with double-buffered TMEM, 3 = kind 2
+ * with every tile split in two along K (where the shape allows); bn 0 = pick.
  * kind -1 restores the automatic choice (also: env B200DP_GEMM_VARIANT=kind[,bn]). */
 int b200_gemm_set_variant(int kind, int bn);
-/* The kernel kind and tile width b200_gemm_bf16 would use for this shape (host-only). */
-int b200_gemm_plan(int M, int N, int rs_on, int both_mn, int* kind, int* bn);
+/* The kernel kind, tile width and K split b200_gemm_bf16 would use for this shape (host-only). */
+int b200_gemm_plan(int M, int N, int K, int rs_on, int both_mn, int* kind, int* bn, int* ksplit);
 /* conv2 forward as a TF32 implicit GEMM on tcgen05 (same contract as b200_conv2_fwd). */
 int b200_conv2_fwd_tc(const float* a1, const float* w, const float* b, float* mask, int mask_mode,
                       float p, unsigned long long seed, unsigned long long step, float* a2,

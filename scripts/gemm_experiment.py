@@ -18,7 +18,7 @@ def t(fn, iters=20, warm=4):
 
 
 dev = torch.device("cuda", 0)
-variants = [("auto", 0), ("cta", 128), ("cta", 256), ("pair", 256), ("pair", 128),
+variants = [("auto", 0), ("cta", 128), ("cta", 256), ("pair", 256), ("pair", 128), ("splitk", 256),
             ("persistent", 256), ("persistent", 128)]
 shapes = [(4096, 4096, 4096), (8192, 8192, 4096), (512, 4096, 4096), (4096, 4096, 512),
           (4096, 784, 512), (512, 4096, 784)]

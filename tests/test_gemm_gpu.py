@@ -60,7 +60,8 @@ def restore_variant():
 
 
 # (kind, bn): the one-tile kernel at its widest tile, the CTA-pair kernel, the persistent kernel
-_VARIANTS = [("cta", 256), ("pair", 256), ("pair", 128), ("persistent", 256), ("persistent", 128)]
+_VARIANTS = [("cta", 256), ("pair", 256), ("pair", 128), ("persistent", 256), ("persistent", 128),
+             ("splitk", 256)]
 
 
 @pytest.mark.parametrize("kind,bn", _VARIANTS)
@@ -115,3 +116,34 @@ def test_gemm_bias_view_with_odd_offset(cuda_device, restore_variant, kind, bn):
     y = gemm.linear_fwd(x, W, b, relu=True)
     want = torch.relu(x.float() @ W.float().t() + b.float())
     torch.testing.assert_close(y.float(), want, rtol=1.6e-2, atol=3e-2)
+
+
+def test_gemm_split_k_repeated_and_epilogues(cuda_device, restore_variant):
+    """Split-K (opt-in variant): the two K halves of a tile run on two CTA pairs; the flags
+    reset themselves, so back-to-back calls keep giving the product."""
+    g = torch.Generator().manual_seed(21)
+    M, N, K = 512, 4096, 4096
+    x = (torch.randn(M, K, generator=g) / 8).to(torch.bfloat16).to(cuda_device)
+    W = (torch.randn(N, K, generator=g) / 8).to(torch.bfloat16).to(cuda_device)
+    b = torch.randn(N, generator=g).to(torch.bfloat16).to(cuda_device)
+    gemm.set_variant("splitk")
+    assert gemm.plan(M, N, K) == ("splitk", 256)
+    want = torch.relu(x.float() @ W.float().t() + b.float())
+    for _ in range(3):
+        y = gemm.linear_fwd(x, W, b, relu=True)
+        torch.testing.assert_close(y.float(), want, rtol=1.6e-2, atol=5e-2)
+    y32 = gemm.linear_fwd(x, W, out_dtype=torch.float32)
+    torch.testing.assert_close(y32, x.float() @ W.float().t(), rtol=2e-3, atol=2e-2)
+    # identical to the unsplit kernel up to fp32 summation order
+    gemm.set_variant("persistent", 256)
+    y_ref = gemm.linear_fwd(x, W, out_dtype=torch.float32)
+    torch.testing.assert_close(y32, y_ref, rtol=1e-4, atol=1e-3)
+    # on a second stream (its own workspace slot), concurrently with the first
+    gemm.set_variant("splitk")
+    s2 = torch.cuda.Stream()
+    s2.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s2):
+        y2 = gemm.linear_fwd(x, W, out_dtype=torch.float32)
+    y1 = gemm.linear_fwd(x, W, out_dtype=torch.float32)
+    torch.cuda.current_stream().wait_stream(s2)
+    assert torch.equal(y1, y2)

@@ -49,23 +49,27 @@ def test_gemm_kernel_plan_host_only(native_lib):
     from csed_514_project_distributed_training_using_pytorch_b200.ops import gemm
     try:
         # the wide-MLP products at per-GPU batch 512 (BASELINE.json config 4)
-        assert gemm.plan(4096, 4096) == ("persistent", 256)             # fc2 wgrad
-        assert gemm.plan(4096, 4096, rs=True, both_mn=True) == ("persistent", 256)
-        assert gemm.plan(4096, 784, rs=True, both_mn=True) == ("persistent", 256)   # fc1 wgrad
-        assert gemm.plan(512, 4096) == ("persistent", 128)              # fc2 forward / dgrad
+        assert gemm.plan(4096, 4096, 512) == ("persistent", 256)        # fc2 wgrad
+        assert gemm.plan(4096, 4096, 512, rs=True, both_mn=True) == ("persistent", 256)
+        assert gemm.plan(4096, 784, 512, rs=True, both_mn=True) == ("persistent", 256)   # fc1 wgrad
+        assert gemm.plan(512, 4096, 4096) == ("persistent", 128)        # fc2 forward / dgrad
+        assert gemm.plan(512, 4096, 784) == ("persistent", 128)         # fc1 forward: K too short
         # the reduce-scatter epilogue of other layouts stays on the one-CTA kernel
-        assert gemm.plan(4096, 4096, rs=True, both_mn=False) == ("cta", 128)
+        assert gemm.plan(4096, 4096, 512, rs=True, both_mn=False) == ("cta", 128)
         # skinny problems: one CTA per tile, tile width follows N
-        assert gemm.plan(64, 4096) == ("cta", 128)
-        assert gemm.plan(4096, 10) == ("cta", 16)
-        assert gemm.plan(512, 40) == ("cta", 64)
+        assert gemm.plan(64, 4096, 4096) == ("cta", 128)
+        assert gemm.plan(4096, 10, 4096) == ("cta", 16)
+        assert gemm.plan(512, 40, 4096) == ("cta", 64)
         # pinning
         gemm.set_variant("pair", 128)
-        assert gemm.plan(4096, 4096) == ("pair", 128)
-        assert gemm.plan(64, 4096)[0] == "cta"                          # pairs need M > 128
+        assert gemm.plan(4096, 4096, 4096) == ("pair", 128)
+        assert gemm.plan(64, 4096, 4096)[0] == "cta"                    # pairs need M > 128
         gemm.set_variant("cta", 256)
-        assert gemm.plan(4096, 4096) == ("cta", 256)
-        assert gemm.plan(100, 100) == ("cta", 128)
+        assert gemm.plan(4096, 4096, 4096) == ("cta", 256)
+        assert gemm.plan(100, 100, 100) == ("cta", 128)
+        gemm.set_variant("splitk")
+        assert gemm.plan(512, 512, 256) == ("splitk", 256)
+        assert gemm.plan(4096, 4096, 4096) == ("persistent", 256)       # too many tiles to split
     finally:
         gemm.set_variant("auto")
-    assert gemm.plan(4096, 4096) == ("persistent", 256)
+    assert gemm.plan(4096, 4096, 4096) == ("persistent", 256)
