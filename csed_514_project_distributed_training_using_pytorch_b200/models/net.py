@@ -17,7 +17,6 @@ from typing import Optional, Tuple
 
 import torch
 import torch.nn as nn
-import torch.nn.functional as F
 
 from ..ops import net_ops
 
@@ -32,11 +31,12 @@ class Net(nn.Module):
         super().__init__()
         # "simt" (fp32-exact) or "tcgen05" (TF32 implicit GEMM on the tensor cores)
         self.conv2_impl = conv2_impl
-        self.conv1 = nn.Conv2d(1, 10, kernel_size=5)
-        self.conv2 = nn.Conv2d(10, 20, kernel_size=5)
-        self.conv2_drop = nn.Dropout2d()
-        self.fc1 = nn.Linear(320, 50)
-        self.fc2 = nn.Linear(50, 10)
+        # Parameter holders, registered in the reference's order (src/model.py:9-13) so that
+        # the state_dict keys and the values drawn under a given torch seed are the same.
+        for name, layer in (("conv1", nn.Conv2d(1, 10, 5)), ("conv2", nn.Conv2d(10, 20, 5)),
+                            ("conv2_drop", nn.Dropout2d(p=0.5)),
+                            ("fc1", nn.Linear(20 * 4 * 4, 50)), ("fc2", nn.Linear(50, 10))):
+            self.add_module(name, layer)
         # Philox key/counter of the CUDA dropout masks (K4, K7): keyed by the torch seed
         # in force at construction unless given, advanced once per training forward.
         self.dropout_seed = int(torch.initial_seed() if dropout_seed is None else dropout_seed) \
@@ -72,14 +72,14 @@ class Net(nn.Module):
         return net_ops.fc2_log_softmax(h1, self.fc2.weight, self.fc2.bias)
 
     def _forward_cpu(self, x, masks):
+        """CPU tensors: the functional oracle (models/oracle.py). With no masks given, training
+        mode applies torch's own dropout ops (so the random stream is the one a stock torch
+        model would consume); eval mode applies none."""
+        from .oracle import net_forward
         x = x.reshape(-1, 1, 28, 28)
         if masks is not None:
-            from .oracle import net_forward
             return net_forward(self.param_list(), x, masks[0], masks[1])
-        x = F.relu(F.max_pool2d(self.conv1(x), 2))
-        x = F.relu(F.max_pool2d(self.conv2_drop(self.conv2(x)), 2))
-        x = x.view(-1, 320)
-        x = F.relu(self.fc1(x))
-        x = F.dropout(x, training=self.training)
-        x = self.fc2(x)
-        return F.log_softmax(x, dim=1)
+        if not self.training:
+            return net_forward(self.param_list(), x)
+        return net_forward(self.param_list(), x, self.conv2_drop,
+                           lambda h: torch.nn.functional.dropout(h, 0.5, True))

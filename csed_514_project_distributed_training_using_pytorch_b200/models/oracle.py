@@ -30,19 +30,25 @@ def make_masks(batch: int, generator: Optional[torch.Generator] = None, p: float
     return m2.to(device), m3.to(device)
 
 
-def net_forward(params: Sequence[torch.Tensor], x: torch.Tensor,
-                m2: Optional[torch.Tensor] = None, m3: Optional[torch.Tensor] = None):
-    """log-probabilities [B,10]. params = (c1w, c1b, c2w, c2b, f1w, f1b, f2w, f2b)."""
+def net_forward(params: Sequence[torch.Tensor], x: torch.Tensor, m2=None, m3=None):
+    """log-probabilities [B,10]. params = (c1w, c1b, c2w, c2b, f1w, f1b, f2w, f2b).
+    m2 / m3: None (no dropout), a mask tensor ([B,20] channel mask / [B,50] element mask,
+    values 0 or 1/(1-p)), or a callable applied to the activation (e.g. a torch dropout
+    module, which keeps torch's own random stream)."""
     c1w, c1b, c2w, c2b, f1w, f1b, f2w, f2b = params
     x = x.view(-1, 1, 28, 28)
     h = F.relu(F.max_pool2d(F.conv2d(x, c1w, c1b), 2))
     h = F.conv2d(h, c2w, c2b)
-    if m2 is not None:
+    if callable(m2):
+        h = m2(h)
+    elif m2 is not None:
         h = h * m2.view(-1, 20, 1, 1)
     h = F.relu(F.max_pool2d(h, 2))
     h = h.reshape(-1, 320)
     h = F.relu(F.linear(h, f1w, f1b))
-    if m3 is not None:
+    if callable(m3):
+        h = m3(h)
+    elif m3 is not None:
         h = h * m3
     h = F.linear(h, f2w, f2b)
     return F.log_softmax(h, dim=1)
