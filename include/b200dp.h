@@ -21,6 +21,9 @@ extern "C" {
 /* ---- runtime -------------------------------------------------------------- */
 const char* b200_last_error(void);
 int b200_version(void);
+/* Used by the library's own translation units to record the message b200_last_error returns
+ * (printf-style); exported so side-by-side builds of single sources can link against it. */
+void b200_set_error(const char* fmt, ...);
 
 /* ---- Net layout / workspace queries ---------------------------------------- */
 /* offsets9[0..7]: float offsets of conv1.w, conv1.b, conv2.w, conv2.b, fc1.w, fc1.b,
@@ -153,6 +156,24 @@ int b200_comm_allreduce(const void* comm, int dtype, int algo, int update, const
                         unsigned* arrive_ctr, float scale, float* master, float* mom,
                         const float* hp, size_t state_base, int blocks, size_t push_from,
                         void* stream);
+
+/* ---- NVLS: in-switch reduction through an NVLink multicast object --------------------- */
+/* Ref: the gradient all-reduce implicit in src/train_dist.py:83; SURVEY §5.1 "NVLS path".
+ * Rank 0 creates the multicast object and exports it as a POSIX fd; the other ranks import
+ * it (the fd travels over a Unix socket, parallel/comm.py); every rank adds its device, then
+ * binds a cuMemCreate allocation and maps both a unicast and a multicast view of it. */
+int b200_nvls_supported(int dev, int* out);
+int b200_nvls_granularity(int world, size_t bytes, size_t* rounded);
+int b200_nvls_create(int world, size_t bytes, unsigned long long* mc_out, int* fd_out);
+int b200_nvls_import(int fd, unsigned long long* mc_out);
+int b200_nvls_add_device(unsigned long long mc, int dev);
+int b200_nvls_bind_map(unsigned long long mc, int dev, size_t bytes, void** uc_ptr, void** mc_ptr);
+/* All-reduce of `bytes` at buf_off inside the NVLS region: multimem.ld_reduce of this rank's
+ * slice, optional fused SGD on the master weights (update = 1), multimem.st of the result. */
+int b200_nvls_allreduce(const void* comm, void* mc_base, size_t buf_off, size_t bytes, int dtype,
+                        size_t flag_off, int gmax, unsigned* seq_ctr, unsigned* arrive_ctr,
+                        float scale, int update, size_t out_off, float* master, float* mom,
+                        const float* hp, size_t state_base, int blocks, void* stream);
 
 /* ---- tcgen05 bf16 GEMM ------------------------------------------------------------------ */
 /* C[M,N] = op(A) op(B)^T, fp32 accumulation in TMEM. a_mn/b_mn select MN-major operands, so

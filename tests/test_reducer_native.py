@@ -73,3 +73,35 @@ def test_gemm_kernel_plan_host_only(native_lib):
     finally:
         gemm.set_variant("auto")
     assert gemm.plan(4096, 4096, 4096) == ("persistent", 256)
+
+
+def test_native_struct_layouts_match_python(native_lib):
+    """ctypes mirrors of native structs have the library's size (host-only ABI check)."""
+    import ctypes as C
+    from csed_514_project_distributed_training_using_pytorch_b200 import _native as N
+    from csed_514_project_distributed_training_using_pytorch_b200.ops.runner import _RunnerConfig
+    lib = N.lib()
+    assert C.sizeof(_RunnerConfig) == lib.b200_runner_config_size()
+    # CommDev is passed by value to every collective kernel: it must fit the 4 KB of kernel
+    # parameters comfortably and hold 8 peer base pointers
+    n = lib.b200_comm_struct_size()
+    assert 8 * 8 <= n <= 512
+
+
+def test_header_declares_every_exported_entry_point(native_lib):
+    """include/b200dp.h is the C contract: every b200_* symbol the library exports is declared
+    there (INTEGRATION.md 'C ABI')."""
+    import re
+    import subprocess
+    from pathlib import Path
+    from csed_514_project_distributed_training_using_pytorch_b200 import _native as N
+    root = Path(__file__).resolve().parents[1]
+    header = (root / "include" / "b200dp.h").read_text()
+    declared = set(re.findall(r"\b(b200_[a-z0-9_]+)\s*\(", header))
+    out = subprocess.run(["nm", "-D", "--defined-only", str(N.lib_path())], capture_output=True, text=True)
+    if out.returncode != 0:
+        pytest.skip("nm is not available")
+    exported = {ln.split()[-1] for ln in out.stdout.splitlines() if " T b200_" in ln}
+    assert exported, "no b200_* symbols exported?"
+    missing = sorted(exported - declared)
+    assert not missing, f"exported but not declared in include/b200dp.h: {missing}"
