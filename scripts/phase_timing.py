@@ -19,13 +19,15 @@ for _ in range(3): eng.step(x, y)
 torch.cuda.synchronize()
 N.call("b200_net_set_phase_debug", None)
 t = buf.view(148, 16)[:2 * B].cpu()
-names = ["start->loaded", "conv1_fwd", "conv2_fwd(+W3 wait)", "fc1_fwd", "fc2_fwd+softmax", "fc2_bwd", "fc1_bwd", "build D", "conv2 wgrad / dgrad T", "gather", "-", "conv1_wgrad", "tail"]
+# stamp k is taken after phase k; stamp 11 is unused (conv1_wgrad runs from stamp 10 to 12)
+phases = [("start->loaded", 0, 1), ("conv1_fwd", 1, 2), ("conv2_fwd(+W3 wait)", 2, 3), ("fc1_fwd", 3, 4),
+          ("fc2_fwd+softmax", 4, 5), ("fc2_bwd", 5, 6), ("fc1_bwd", 6, 7), ("build D", 7, 8),
+          ("conv2 wgrad / dgrad T", 8, 9), ("gather", 9, 10), ("conv1_wgrad", 10, 12), ("tail", 12, 13)]
 for role in (0, 1):
     rows = t[role::2]
-    d = rows[:, 1:14] - rows[:, 0:13]
     print(f"role {role}: total cycles median {float((rows[:,13]-rows[:,0]).double().median()):.0f}")
-    for i, n in enumerate(names):
-        col = d[:, i].double()
-        if (role == 0 and i >= 9) or n == '-': continue
+    for n, a, b in phases:
+        if role == 0 and a >= 9: continue      # role 0 stops after the conv2 weight gradient
+        col = (rows[:, b] - rows[:, a]).double()
         print(f"   {n:22s} median {float(col.median()):8.0f}  max {float(col.max()):8.0f}")
 
