@@ -49,7 +49,7 @@ _SIGS = {
     "b200_nll_bwd": [c_p, c_p, c_p, c_i, c_i, c_p],
     "b200_sgd_momentum": [c_p, c_p, c_p, c_ll, c_p, c_f, c_p],
     "b200_net_fwdbwd": [c_p, c_p, c_i, c_p, c_p, c_i, c_p, c_p, c_i, c_p, c_p, c_ull, c_p, c_u, c_i,
-                        c_p],
+                        c_i, c_p],
     "b200_net_reduce_sgd": [c_p, c_i, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_p, c_p],
     "b200_net_eval": [c_p, c_p, c_i, c_p, c_p, c_i, c_p, c_p, c_p, c_p, c_i, c_p],
 }

@@ -103,7 +103,8 @@ class FusedNetEngine:
             mode, m2, m3 = 0, None, None
         N.call("b200_net_fwdbwd", N.ptr(self.flat.param), N.ptr(x), x_mode, N.ptr(y), N.ptr(gidx),
                B, N.ptr(self.partial), N.ptr(self.loss_partial), mode, N.ptr(m2), N.ptr(m3),
-               self.seed, N.ptr(self.step_ctr), self.sample_base, int(idx_stride), N.stream())
+               self.seed, N.ptr(self.step_ctr), self.sample_base, int(idx_stride),
+               int(gidx.numel()) if gidx is not None else 0, N.stream())
         self.launches += 1
         return B
 
@@ -161,6 +162,16 @@ class FusedNetEngine:
         g.kernels_per_replay = self.launches - launches_before
         g.steps_per_replay = max(1, unroll)
         self.launches = launches_before
+        # First launch of an instantiated graph uploads it to the device (tens of
+        # microseconds for a 32-kernel graph). Pay that here, not in the caller's first
+        # timed replay: one throw-away replay with the training state put back afterwards.
+        # Every rank captures at the same point, so the collective inside kernel B matches.
+        with torch.cuda.stream(s):
+            saved = self._snapshot()
+            g.replay()
+            self._restore(saved)
+        torch.cuda.current_stream().wait_stream(s)
+        torch.cuda.synchronize(self.device)
         if key is not None:
             self._graphs[key] = g
         return g

@@ -130,6 +130,15 @@ class DataParallel(nn.Module):
             self.reducer.finalize_backward()
             self._pass_open = False
 
+    def finish_backward(self):
+        """Call after `loss.backward()`: if a parameter received no gradient in this pass its
+        bucket never filled, so launch what is still pending (zeros for that parameter, like
+        torch DDP's find_unused_parameters) and join the reducer stream. A no-op when every
+        bucket was launched from the hooks."""
+        if self._pass_open:
+            self.reducer.finalize_backward()
+            self._pass_open = False
+
     @contextlib.contextmanager
     def no_sync(self):
         """Accumulate gradients locally (no all-reduce) inside the context."""

@@ -46,9 +46,9 @@ def init_process_group(backend: str = "auto", rank: Optional[int] = None,
     cpu_group = None
     if world_size > 1 or dist.is_initialized():
         if not dist.is_initialized():
-            # gloo carries the bootstrap objects; nccl is registered only so baselines
-            # (bench/allreduce_sweep.py) can be timed in the same process. It is lazy.
-            tb = "cpu:gloo,cuda:nccl" if backend == "b200" else "gloo"
+            # gloo carries the bootstrap objects only (rendezvous, handle exchange). Scripts
+            # that time an NCCL baseline create their own NCCL group (scripts/_nccl.py).
+            tb = "gloo"
             if backend == "b200":
                 local = int(env.get("LOCAL_RANK", rank))
                 torch.cuda.set_device(local if device is None else torch.device(device))

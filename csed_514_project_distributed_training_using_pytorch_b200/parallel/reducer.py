@@ -21,6 +21,7 @@ from typing import List, Optional, Sequence
 import torch
 
 from .. import _native as N
+from ..utils import nvtx
 
 c_p, c_i, c_ll = C.c_void_p, C.c_int, C.c_longlong
 N.register_sigs({
@@ -220,6 +221,7 @@ class Reducer:
         g = self.flat.grad[lo:hi]
         nbytes = (hi - lo) * g.element_size()
         algo = self._algo_for(nbytes)
+        nvtx.push(f"bucket {b} all-reduce ({nbytes} B, algo {algo})")
         if self.is_cuda:
             self.stream.wait_stream(torch.cuda.current_stream())
             ctx = torch.cuda.stream(self.stream)
@@ -245,6 +247,7 @@ class Reducer:
                     master.sub_(lr * mom)
                     if master.data_ptr() != self.flat.param[lo:hi].data_ptr():
                         self.flat.param[lo:hi].copy_(master)
+        nvtx.pop()
         self.kernel_launches += 1
         self.launched.append(b)
 

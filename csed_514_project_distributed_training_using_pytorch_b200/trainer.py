@@ -36,6 +36,7 @@ from .utils.data import MNISTArrays, load_mnist
 from .utils.flat import FlatParams
 from .utils.metrics import MetricsLogger
 from .utils.sampler import ShardSampler
+from .utils import nvtx
 
 
 class Trainer:
@@ -47,6 +48,10 @@ class Trainer:
         self.world = comm.world_size if comm is not None else 1
         self.distributed_style = (self.world > 1 or comm is not None) \
             if distributed_style is None else distributed_style
+        if comm is not None:
+            # the per-rank batch is int(batch / world) of the REAL world (src/train_dist.py:134),
+            # whatever the config object was built with
+            cfg.world_size, cfg.rank = self.world, self.rank
         use_cuda = cfg.device != "cpu" and torch.cuda.is_available()
         if cfg.device != "cpu" and not use_cuda:
             raise RuntimeError("device='cuda' requested but no GPU is visible; pass device='cpu'")
@@ -90,7 +95,8 @@ class Trainer:
         self.examples_seen = 0
         self.native_runner = True   # host-streaming steps go through csrc/runner.cu
         if cfg.resume:
-            self.resume(cfg.resume)
+            # momentum lives in optimizer.pth beside model.pth (src/train.py:84-85)
+            self.resume(cfg.resume, os.path.join(os.path.dirname(cfg.resume) or ".", "optimizer.pth"))
 
     # ------------------------------------------------------------------ data
     def set_data(self, train: MNISTArrays, test: Optional[MNISTArrays] = None):
@@ -149,11 +155,12 @@ class Trainer:
         self.model.train()
         sampler = self._sampler()
         sampler.set_epoch(epoch if self.distributed_style else epoch - 1)
-        if self.device.type == "cuda" and self.engine is not None:
-            if self.cfg.feed == "host":
-                return self._train_epoch_host_feed(epoch, sampler)
-            return self._train_epoch_fused(epoch, sampler)
-        return self._train_epoch_autograd(epoch, sampler)
+        with nvtx.range(f"train_epoch {epoch}"):
+            if self.device.type == "cuda" and self.engine is not None:
+                if self.cfg.feed == "host":
+                    return self._train_epoch_host_feed(epoch, sampler)
+                return self._train_epoch_fused(epoch, sampler)
+            return self._train_epoch_autograd(epoch, sampler)
 
     def _train_epoch_host_feed(self, epoch: int, sampler: ShardSampler) -> float:
         """Dataset stays on the host: gather this epoch's order into pinned memory once, then
@@ -247,6 +254,8 @@ class Trainer:
                 elif bi % li == 0:
                     self.log.train_log(epoch, bi, blen, n_dataset, n_batches, l,
                                        bi * 64 + (epoch - 1) * n_dataset)
+            if self.distributed_style and losses:
+                self.log.progress(upto_batch, n_batches, losses[-1], final=upto_batch >= n_batches)
             pending = 0
 
         chunk = min(eng.ring - self.UNROLL, max(li, 256))
@@ -254,16 +263,16 @@ class Trainer:
         while bi < full:
             if g_multi is not None and full - bi >= self.UNROLL:
                 g_multi.replay()
-                n = self.UNROLL
+                adv = self.UNROLL
             elif g_full is not None:
                 g_full.replay()
-                n = 1
+                adv = 1
             else:
                 eng.step(data.images, data.labels, X_U8_GATHER, gidx=self._perm_dev, batch=B,
                          idx_stride=B)
-                n = 1
-            bi += n
-            pending += n
+                adv = 1
+            bi += adv
+            pending += adv
             if pending >= chunk:
                 flush(bi)
                 if not self.distributed_style and c.checkpoint_every_log:
@@ -301,6 +310,9 @@ class Trainer:
             out = fwd(x)
             loss = net_ops.nll_loss(out, y)
             loss.backward()
+            if self.ddp is not None:
+                # launches any bucket a parameter without gradient kept from filling
+                self.ddp.finish_backward()
             if self.ddp is not None and self.device.type == "cuda":
                 torch.cuda.current_stream().wait_stream(self.ddp.reducer.stream)
             self.opt.step()
@@ -325,6 +337,7 @@ class Trainer:
         src/train_dist.py:21-24,92-104). Returns (nll_sum, correct, n, sum_of_batch_means)."""
         self.model.eval()
         c = self.cfg
+        nvtx.push("evaluate")
         data = self._resident("test")
         n = len(data)
         Bt = c.batch_size_test
@@ -349,6 +362,7 @@ class Trainer:
                 sum_means += l / x.shape[0]
                 correct += int((out.argmax(1) == y).sum().item())
         self.model.train()
+        nvtx.pop()
         return nll_sum, correct, n, sum_means
 
     # -------------------------------------------------------------------- fit
@@ -374,6 +388,9 @@ class Trainer:
             self.log.save_curves(c.images_dir, "train_test_curve_dist")
         else:
             self.log.test_counter = [i * n_train for i in range(epochs + 1)]  # src/train.py:67
+            if self.test_set is not None and len(self.test_set) >= 6:         # src/train.py:43-57
+                self.log.save_sample_digits(c.images_dir, self.test_set.images[:6].cpu().numpy(),
+                                            self.test_set.labels[:6].tolist())
             nll_sum, correct, n, _ = self.evaluate()                           # src/train.py:106
             self.log.test_log(nll_sum / n, correct, n)
             for epoch in range(1, epochs + 1):
@@ -394,7 +411,13 @@ class Trainer:
         if eng is None:
             raise RuntimeError("train_steps_from_host needs the fused CUDA engine")
         if loss_out is None:
-            loss_out = torch.empty(steps, dtype=torch.float32).pin_memory()
+            # one pinned buffer per trainer, grown on demand: pinning memory is a blocking
+            # driver call that must not sit in the step loop. The returned view is
+            # overwritten by the next call; pass loss_out to keep several results.
+            buf = getattr(self, "_loss_pinned", None)
+            if buf is None or buf.numel() < steps:
+                buf = self._loss_pinned = torch.empty(max(steps, 1024), dtype=torch.float32).pin_memory()
+            loss_out = buf[:steps]
         if self.cfg.cuda_graph and self.native_runner:
             # native loop (csrc/runner.cu): per-step copies, 16-step kernel graphs, no Python
             key = ("runner", batch, hx.dtype)

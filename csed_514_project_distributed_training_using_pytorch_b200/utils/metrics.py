@@ -64,6 +64,65 @@ class MetricsLogger:
         self._emit({"kind": "epoch", "epoch": epoch, "train_loss": train_loss,
                     "val_loss": val_loss, "accuracy": accuracy})
 
+    def progress(self, done: int, total: int, loss: float, final: bool = False):
+        """The reference's tqdm bar text, `training batch_loss=...` (src/train_dist.py:76,87).
+        Losses reach the host once per flush of the device ring, so the line advances per
+        flush, not per batch. Written to stderr like tqdm; silent when quiet or rank != 0."""
+        if self.rank != 0 or self.quiet:
+            return
+        import sys
+        pct = 100.0 * done / max(1, total)
+        rate = done / max(1e-9, self.elapsed())
+        sys.stderr.write(f"\rtraining batch_loss={loss:.4f}: {pct:3.0f}%| {done}/{total} "
+                         f"[{self.elapsed():.1f}s, {rate:.1f}it/s]" + ("\n" if final else ""))
+        sys.stderr.flush()
+
+    def save_sample_digits(self, images_dir: str, images_u8, labels, name: str = "train_images"):
+        """The reference's 2x3 figure of six test digits with their ground truth
+        (src/train.py:43-57). Without matplotlib the same content is written as
+        `<name>.npy` (uint8 [6,28,28]), `<name>_labels.csv` and a 2x3 montage `<name>.pgm`
+        (plain binary PGM, viewable anywhere); the PNG with titles is added when matplotlib
+        imports."""
+        if self.rank != 0:
+            return None
+        import numpy as np
+        os.makedirs(images_dir, exist_ok=True)
+        imgs = np.asarray(images_u8[:6], dtype=np.uint8).reshape(-1, 28, 28)
+        labs = [int(x) for x in list(labels[:6])]
+        np.save(os.path.join(images_dir, name + ".npy"), imgs)
+        with open(os.path.join(images_dir, name + "_labels.csv"), "w", newline="") as f:
+            w = csv.writer(f)
+            w.writerow(["panel", "ground_truth"])
+            for i, l in enumerate(labs):
+                w.writerow([i, l])
+        n = imgs.shape[0]
+        rows = (n + 2) // 3
+        canvas = np.zeros((rows * 30 + 2, 3 * 30 + 2), dtype=np.uint8)
+        for i in range(n):
+            r, c = divmod(i, 3)
+            canvas[2 + r * 30:2 + r * 30 + 28, 2 + c * 30:2 + c * 30 + 28] = imgs[i]
+        path = os.path.join(images_dir, name + ".pgm")
+        with open(path, "wb") as f:
+            f.write(b"P5\n%d %d\n255\n" % (canvas.shape[1], canvas.shape[0]))
+            f.write(canvas.tobytes())
+        try:
+            import matplotlib
+            matplotlib.use("Agg")
+            import matplotlib.pyplot as plt
+            fig = plt.figure()
+            for i in range(n):
+                plt.subplot(2, 3, i + 1)
+                plt.tight_layout()
+                plt.imshow(imgs[i], cmap="gray", interpolation="none")
+                plt.title("Ground Truth: {}".format(labs[i]))
+                plt.xticks([])
+                plt.yticks([])
+            fig.savefig(os.path.join(images_dir, name + ".png"))
+            plt.close(fig)
+        except Exception:
+            pass
+        return path
+
     def save_curves(self, images_dir: str, name: str = "train_test_curve"):
         """CSV always; PNG if matplotlib is importable."""
         if self.rank != 0:

@@ -4,8 +4,9 @@ semantics pinned from torch/utils/data/distributed.py:102-134).
 num_samples = ceil(N / world); total = num_samples * world; the epoch's permutation is
 randperm(N) from a generator seeded with seed + epoch; it is padded by wrapping (or cut when
 drop_last) to `total`; rank r takes indices[r:total:world]. The output is bit-equal to
-torch's sampler (tests/test_sampler.py) but comes back as one int32 tensor, ready to be
-uploaded once per epoch for the device-side gather.
+torch's sampler (tests/test_cpu_core.py::test_sampler_bit_parity_with_torch) and comes back as
+one int64 CPU tensor; the trainer converts it to int32 and uploads it once per epoch for the
+device-side gather.
 """
 from __future__ import annotations
 

@@ -502,7 +502,7 @@ net_fwdbwd_kernel(const float* __restrict__ params, const void* __restrict__ x, 
                   float inv_B, float* __restrict__ partial, float* __restrict__ loss_partial,
                   int mask_mode, float* __restrict__ m2buf, float* __restrict__ m3buf,
                   unsigned long long seed, const unsigned long long* __restrict__ step_ptr,
-                  unsigned sample_base, int idx_stride, int split) {
+                  unsigned sample_base, int idx_stride, int split, int n_idx) {
   extern __shared__ __align__(16) float smem[];
   const FusedSmem f = carve(smem);
   float* Ds = smem + FUSED_SMEM_FLOATS;
@@ -544,7 +544,10 @@ net_fwdbwd_kernel(const float* __restrict__ params, const void* __restrict__ x, 
   for (int i = t; i < W3_SZ / 4; i += NT) cp16(w3s + 4 * i, params + OFF_W3 + 4 * i);
   asm volatile("cp.async.commit_group;" ::: "memory");
   const unsigned long long step = step_ptr ? step_ptr[0] : 0ull;
-  if (idx_stride != 0 && step_ptr) gidx += (size_t)(step - step_ptr[1]) * (size_t)idx_stride;
+  // indices of THIS step start at idx_base; n_idx bounds the prefetch of the next step's rows
+  const long long idx_base =
+      (idx_stride != 0 && step_ptr) ? (long long)(step - step_ptr[1]) * (long long)idx_stride : 0ll;
+  gidx += idx_base;
   float* row = partial + (size_t)slot * FLAT_SZ;
   float loss_acc = 0.0f;
   int it = 0;
@@ -632,7 +635,9 @@ net_fwdbwd_kernel(const float* __restrict__ params, const void* __restrict__ x, 
     const int* nidx = gidx + idx_stride;
     const size_t row_bytes = (x_mode == 3) ? IMG_SZ * 4 : IMG_SZ;
     const int lines = (int)((row_bytes + 127) / 128);
-    for (int img = slot; img < B; img += nslots)
+    // never read an index beyond the end of the permutation (last step of an epoch)
+    const long long left = (long long)n_idx - (idx_base + idx_stride);
+    for (int img = slot; img < B && img < left; img += nslots)
       if (t < lines) {
         const char* p = (const char*)x + (size_t)nidx[img] * row_bytes + (size_t)t * 128;
         asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
@@ -936,8 +941,10 @@ int b200_net_fwdbwd(const float* params, const void* x, int x_mode, const long l
                     const int* gidx, int B, float* partial, float* loss_partial, int mask_mode,
                     float* m2buf, float* m3buf, unsigned long long seed,
                     const unsigned long long* step_ptr, unsigned sample_base, int idx_stride,
-                    void* stream) {
+                    int n_idx, void* stream) {
   B200_REQUIRE(B > 0, "b200_net_fwdbwd: empty batch");
+  B200_REQUIRE(idx_stride == 0 || n_idx > 0,
+               "b200_net_fwdbwd: device-side index stepping needs the length of the index buffer");
   B200_REQUIRE(mask_mode != 2 || (m2buf && m3buf), "b200_net_fwdbwd: mask_mode 2 needs both masks");
   B200_REQUIRE(x_mode < 2 || gidx != nullptr, "b200_net_fwdbwd: gather modes need an index buffer");
   if (int e = ensure_fused_attr()) return e;
@@ -947,7 +954,7 @@ int b200_net_fwdbwd(const float* params, const void* x, int x_mode, const long l
   B200_CUDA_OK(b200_launch_pdl(net_fwdbwd_kernel, dim3(grid), dim3(NT), FUSED_SMEM_BYTES,
                                (cudaStream_t)stream, b200_pdl_enabled(), params, x, x_mode, labels,
                                gidx, B, 1.0f / (float)B, partial, loss_partial, mask_mode, m2buf,
-                               m3buf, seed, step_ptr, sample_base, idx_stride, split));
+                               m3buf, seed, step_ptr, sample_base, idx_stride, split, n_idx));
   return 0;
 }
 

@@ -40,7 +40,7 @@ int b200_net_fwdbwd(const float* params, const void* x, int x_mode, const long l
                     const int* gidx, int B, float* partial, float* loss_partial, int mask_mode,
                     float* m2buf, float* m3buf, unsigned long long seed,
                     const unsigned long long* step_ptr, unsigned sample_base, int idx_stride,
-                    void* stream);
+                    int n_idx, void* stream);
 int b200_net_reduce_sgd(const float* partial, int rows, float* params, float* mom, float* grad_out,
                         const float* hp, const float* loss_partial, float* loss_ring, int ring,
                         unsigned long long* step_ptr, void* stream);
@@ -105,7 +105,7 @@ int launch_step(Runner* r, const void* x, const long long* y, cudaStream_t s) {
   const RunnerConfig& c = r->cfg;
   int e = b200_net_fwdbwd(c.params, x, c.x_mode, y, nullptr, c.batch, c.partial,
                           c.loss_partial, c.mask_mode, nullptr, nullptr, c.seed, c.ctl,
-                          c.sample_base, 0, s);
+                          c.sample_base, 0, 0, s);
   if (e) return e;
   const int rows = b200_net_fused_rows(c.batch);
   if (c.multi)
@@ -132,6 +132,8 @@ int capture_steps(Runner* r, const char* x, const long long* y, int n, cudaGraph
   B200_CUDA_OK(ce);
   B200_CUDA_OK(cudaGraphInstantiate(out, g, 0));
   B200_CUDA_OK(cudaGraphDestroy(g));
+  // upload now: otherwise the first cudaGraphLaunch pays for it inside the caller's loop
+  B200_CUDA_OK(cudaGraphUpload(*out, r->compute));
   return 0;
 }
 

@@ -93,12 +93,13 @@ int b200_sgd_momentum(float* p, const float* g, float* buf, long long n, const f
  * x_mode 0 fp32 [B,784]; 1 uint8 [B,784]; 2 uint8 dataset gathered by gidx; 3 fp32 dataset
  * gathered by gidx. partial: [rows][21848] floats; loss_partial: [rows].
  * step_ptr (device u64[2]) = {optimizer step, step at epoch start}; idx_stride != 0 makes the
- * batch's indices gidx[(step - epoch_start) * idx_stride ...]. Ref: src/train.py:72-75 */
+ * batch's indices gidx[(step - epoch_start) * idx_stride ...]; n_idx is then the length of
+ * gidx (the next step's rows are prefetched only while they exist). Ref: src/train.py:72-75 */
 int b200_net_fwdbwd(const float* params, const void* x, int x_mode, const long long* labels,
                     const int* gidx, int B, float* partial, float* loss_partial, int mask_mode,
                     float* m2buf, float* m3buf, unsigned long long seed,
                     const unsigned long long* step_ptr, unsigned sample_base, int idx_stride,
-                    void* stream);
+                    int n_idx, void* stream);
 /* Kernel B (1 GPU): fixed-order row sum + SGD-momentum; loss -> loss_ring[step % ring] and
  * loss_ring[ring]; advances step_ptr[0]. Ref: src/train.py:76 */
 int b200_net_reduce_sgd(const float* partial, int rows, float* params, float* mom, float* grad_out,

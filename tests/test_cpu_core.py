@@ -189,3 +189,55 @@ def test_trainer_cpu_learns_and_writes_reference_artifacts(tmp_path, capsys):
     tr2.load_data()
     a = tr.evaluate(); b = tr2.evaluate()
     assert a[1] == b[1] and abs(a[0] - b[0]) < 1e-3
+
+
+def test_sample_digit_figure_and_progress(tmp_path, capsys):
+    """src/train.py:43-57 (six test digits with ground truth) and src/train_dist.py:76,87
+    (tqdm text with the batch loss): both have a file/stream form that needs no matplotlib."""
+    import numpy as np
+    from csed_514_project_distributed_training_using_pytorch_b200.utils.data import synthetic_mnist
+    from csed_514_project_distributed_training_using_pytorch_b200.utils.metrics import MetricsLogger
+    d = synthetic_mnist(8, seed=3)
+    log = MetricsLogger(rank=0)
+    p = log.save_sample_digits(str(tmp_path), d.images[:6].numpy(), d.labels[:6].tolist())
+    arr = np.load(tmp_path / "train_images.npy")
+    assert arr.shape == (6, 28, 28) and arr.dtype == np.uint8
+    assert (arr.reshape(6, 784) == d.images[:6].numpy()).all()
+    head = open(p, "rb").read(15)
+    assert head.startswith(b"P5\n92 62\n255\n")
+    rows = open(tmp_path / "train_images_labels.csv").read().strip().splitlines()
+    assert rows[0] == "panel,ground_truth" and len(rows) == 7
+    log.progress(10, 100, 2.25)
+    log.progress(100, 100, 0.5, final=True)
+    err = capsys.readouterr().err
+    assert "training batch_loss=2.2500" in err and "100/100" in err
+    assert MetricsLogger(rank=1).save_sample_digits(str(tmp_path), d.images[:6].numpy(), [0] * 6) is None
+
+
+def test_nvtx_ranges_balance_and_noop_on_cpu():
+    from csed_514_project_distributed_training_using_pytorch_b200.utils import nvtx
+    with nvtx.range("outer"):
+        nvtx.push("inner")
+        nvtx.pop()
+    nvtx.pop()          # an extra pop must not underflow
+    assert nvtx.depth() == 0
+
+
+def test_trainer_takes_world_from_comm_not_config():
+    """Trainer(TrainConfig(), comm) must use int(64 / comm.world_size) per rank
+    (src/train_dist.py:134), not the config's default world_size of 1."""
+    from csed_514_project_distributed_training_using_pytorch_b200.trainer import Trainer
+    from csed_514_project_distributed_training_using_pytorch_b200.utils.config import TrainConfig
+
+    class FakeComm:
+        rank, world_size = 1, 4
+        device = torch.device("cpu")
+        def alloc(self, numel, dtype=torch.float32, device=None):
+            return torch.zeros(numel, dtype=dtype)
+        def all_gather_object(self, o):
+            return [o] * 4
+        def broadcast(self, t, root=0):
+            return t
+    cfg = TrainConfig(device="cpu")
+    tr = Trainer(cfg, comm=FakeComm())
+    assert tr.cfg.world_size == 4 and tr.cfg.rank_batch() == 16
