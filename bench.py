@@ -46,6 +46,8 @@ def parse():
     ap.add_argument("--input", default="f32", choices=["f32", "u8"],
                     help="dtype of the images copied host->device in the e2e run")
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--no-persist", action="store_true",
+                    help="two-kernel step in 16-step CUDA graphs instead of the persistent kernel")
     ap.add_argument("--skip-e2e", action="store_true")
     ap.add_argument("--ref-cudnn", default="both", choices=["both", "on", "off"])
     return ap.parse_args()
@@ -115,6 +117,9 @@ def run_ours(a):
                       per_rank_batch=a.batch, world_size=world, rank=rank,
                       cuda_graph=not a.no_graph)
     tr = Trainer(cfg, comm=comm, distributed_style=True)
+    if a.no_persist:
+        tr.persistent = False
+    persistent = tr.persistent
     eng = tr.engine
     B, K, W = a.batch, a.steps, a.warmup
 
@@ -126,7 +131,9 @@ def run_ours(a):
     perm = perm.to(torch.int32).to(dev)
     steps_per_epoch = shard // B
     U = 16   # steps per captured graph (programmatic dependent launch spans step boundaries)
-    if a.no_graph:
+    if persistent:
+        one = multi = None
+    elif a.no_graph:
         def one():
             eng.step(dx, dy, X_F32_GATHER, gidx=perm, batch=B, idx_stride=B)
         multi = None
@@ -140,6 +147,9 @@ def run_ours(a):
             eng.begin_epoch()
             m = min(steps_per_epoch, n - done)
             i = 0
+            if persistent:   # every step of this stretch in ONE launch of the persistent kernel
+                eng.run_steps(dx, dy, X_F32_GATHER, gidx=perm, batch=B, nsteps=m, idx_stride=B)
+                i = m
             while i < m:
                 if multi is not None and m - i >= U:
                     multi(); i += U
@@ -152,21 +162,32 @@ def run_ours(a):
         if comm is not None:
             comm.host_barrier()
 
+    def aligned_start(ev):
+        """Ranks leave a host barrier tens of microseconds apart, which is several percent of a
+        0.5 ms timed region: line them up on the device with the peer-memory barrier kernel
+        and record the start event behind it."""
+        if comm is not None:
+            comm.barrier()
+        ev.record()
+
     sampler = ClockSampler(local, period_s=0.05).start() if rank == 0 else None
     run_steps(W)
     sync_all()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
+    l0 = eng.launches
+    aligned_start(e0)
     run_steps(K)
     e1.record()
     sync_all()
     ms = e0.elapsed_time(e1)
+    if persistent:
+        eng.check_errors()
     if comm is not None:
         comm.check_errors()
         ms = comm.max_over_ranks(ms)
     value = K * B * world / (ms / 1e3)
-    kernels_per_step = 2
-    launches = K * kernels_per_step
+    launches = eng.launches - l0 if (persistent or a.no_graph) else K * 2
+    kernels_per_step = launches / K
 
     # ---- end to end through the public API: pinned host -> device per step, loss -> host per step
     e2e = None
@@ -175,15 +196,21 @@ def run_ours(a):
             hx, _ = synthetic_host_dataset(rank, "u8")
         hxp, hyp = hx.pin_memory(), hy.pin_memory()
         n_avail = N_TRAIN // B
-        def host_steps(n, out=None):
+        loss_pinned = torch.empty(max(K, W, 3), dtype=torch.float32).pin_memory()
+
+        def host_steps(n):
             done, outs = 0, []
             while done < n:
                 m = min(n_avail, n - done)
-                outs.append(tr.train_steps_from_host(hxp, hyp, m, B))
+                outs.append(tr.train_steps_from_host(hxp, hyp, m, B,
+                                                     loss_out=loss_pinned[done:done + m]))
                 done += m
             return outs
         host_steps(max(W, 3))
         sync_all()
+        if comm is not None:
+            comm.barrier()
+            torch.cuda.synchronize()
         t0 = time.perf_counter()
         e0.record()
         losses = host_steps(K)
@@ -198,13 +225,22 @@ def run_ours(a):
                "h2d_bytes_per_step": B * 784 * hxp.element_size() + B * 8,
                "d2h_bytes_per_step": 4, "input_dtype": a.input, "last_loss": last,
                "api": "Trainer.train_steps_from_host",
-               "submission": "every step: its own H2D copies (images, labels) and its own D2H "
-                             "copy of the loss; the kernels of 16 consecutive steps form one graph"}
+               "submission": ("every step: its own H2D copies (images, labels) on a copy stream, a "
+                              "32-bit stream write that tells the running persistent kernel the "
+                              "batch has landed, and a 4-byte store of the step's loss by the kernel "
+                              "into the caller's pinned buffer; one kernel launch per call")
+               if persistent else
+               ("every step: its own H2D copies (images, labels) and its own D2H copy of the "
+                "loss; the kernels of 16 consecutive steps form one graph")}
     clocks = sampler.stop() if sampler is not None else None
     if rank == 0:
         result_line(a, "ours", value, ms / K, e2e, clocks, launches,
-                    {"cuda_graph": not a.no_graph, "steps_per_graph": 1 if a.no_graph else U,
+                    {"engine": "persistent kernel (csrc/net_persist.cu)" if persistent
+                     else "two kernels per step in CUDA graphs",
+                     "cuda_graph": (not a.no_graph) and not persistent,
+                     "steps_per_launch": K if persistent else (1 if a.no_graph else U),
                      "kernels_per_step": kernels_per_step,
+                     "timed_region_start": "in-stream peer barrier on every rank, then the start event",
                      "last_losses": eng.last_losses(2).tolist()})
     if comm is not None:
         P.destroy_process_group()

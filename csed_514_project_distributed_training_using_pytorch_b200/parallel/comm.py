@@ -559,9 +559,10 @@ class PeerComm(BaseComm):
         return out_t
 
     # -- fused Net kernel B ------------------------------------------------------
-    def reduce_allreduce_sgd(self, eng, rows: int, write_grad: bool = False, update: bool = True):
-        """Partial-row sum + one-shot all-reduce + 1/world + SGD-momentum in ONE kernel
-        (SURVEY K17+K15) for ops.fused.FusedNetEngine."""
+    def net_channel(self) -> dict:
+        """Staging, flags and sequence counter of the Net gradient exchange (collective on
+        first use: every rank must reach it). Shared by kernel B of the two-kernel step and by
+        the persistent kernel, whose tagged words carry the same sequence numbers."""
         if self._net is None:
             self._net = {
                 "stage": self._region(self.lib.b200_comm_net_stage_bytes()),
@@ -570,7 +571,12 @@ class PeerComm(BaseComm):
             }
             torch.cuda.synchronize(self.device)
             self.host_barrier()
-        n = self._net
+        return self._net
+
+    def reduce_allreduce_sgd(self, eng, rows: int, write_grad: bool = False, update: bool = True):
+        """Partial-row sum + one-shot all-reduce + 1/world + SGD-momentum in ONE kernel
+        (SURVEY K17+K15) for ops.fused.FusedNetEngine."""
+        n = self.net_channel()
         N.check(self.lib.b200_comm_net_reduce_allreduce_sgd(
             self._blob, N.ptr(eng.partial), rows,
             N.ptr(eng.flat.param) if update else None,

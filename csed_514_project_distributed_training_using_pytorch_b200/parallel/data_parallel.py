@@ -155,10 +155,12 @@ class DataParallel(nn.Module):
         self.flat.rebind_grads()
 
     def fused_engine(self, lr: float, momentum: float, seed: int = 1, **kw):
-        """The two-kernel fused step for models.Net with the all-reduce inside kernel B."""
-        from ..ops.fused import FusedNetEngine
-        return FusedNetEngine(self.module, lr=lr, momentum=momentum, seed=seed, comm=self.comm,
-                              flat=self.flat, **kw)
+        """The fused engine for models.Net: the persistent step kernel (gradient exchange
+        overlapped with backward, csrc/net_persist.cu) plus the two-kernel step with the
+        all-reduce inside kernel B."""
+        from ..ops.persist import PersistentNetEngine
+        return PersistentNetEngine(self.module, lr=lr, momentum=momentum, seed=seed,
+                                   comm=self.comm, flat=self.flat, **kw)
 
     def state_dict(self, *a, **k):
         """The UNWRAPPED module's state_dict: no `module.` prefix (src/train_dist.py:116,164)."""

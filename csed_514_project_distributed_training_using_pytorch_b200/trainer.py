@@ -29,6 +29,7 @@ import torch
 from .models import Net
 from .ops import net_ops
 from .ops.fused import FusedNetEngine, X_F32, X_U8, X_U8_GATHER
+from .ops.persist import PersistentNetEngine, persistent_enabled
 from .ops.sgd import FlatSGD
 from .utils import checkpoint as ckpt
 from .utils.config import TrainConfig
@@ -74,8 +75,8 @@ class Trainer:
                 self.engine = self.ddp.fused_engine(cfg.learning_rate, cfg.momentum,
                                                     seed=cfg.random_seed, dropout=cfg.dropout)
             else:
-                self.engine = FusedNetEngine(self.model, cfg.learning_rate, cfg.momentum,
-                                             seed=cfg.random_seed, dropout=cfg.dropout)
+                self.engine = PersistentNetEngine(self.model, cfg.learning_rate, cfg.momentum,
+                                                  seed=cfg.random_seed, dropout=cfg.dropout)
             self.flat = self.engine.flat
         else:
             if comm is not None and self.world > 1:
@@ -93,7 +94,10 @@ class Trainer:
         self._graphs = {}
         self._perm_dev = None
         self.examples_seen = 0
-        self.native_runner = True   # host-streaming steps go through csrc/runner.cu
+        self.native_runner = True   # host-streaming steps go through native code, not Python
+        # persistent step kernel (csrc/net_persist.cu) for whole runs of steps; the two-kernel
+        # graphs remain for B200DP_PERSIST=0 and for cuda_graph=False debugging
+        self.persistent = persistent_enabled() and isinstance(self.engine, PersistentNetEngine)
         if cfg.resume:
             # momentum lives in optimizer.pth beside model.pth (src/train.py:84-85)
             self.resume(cfg.resume, os.path.join(os.path.dirname(cfg.resume) or ".", "optimizer.pth"))
@@ -178,13 +182,19 @@ class Trainer:
         n_dataset = len(self.train_set)
         batches = sampler.batches(B)
         losses = []
+        if getattr(self, "_epoch_loss_pinned", None) is None or self._epoch_loss_pinned.numel() < full + 1:
+            self._epoch_loss_pinned = torch.empty(full + 1, dtype=torch.float32).pin_memory()
         if full:
-            losses.append(self.train_steps_from_host(self._host_x, self._host_y, full, B))
+            losses.append(self.train_steps_from_host(self._host_x, self._host_y, full, B,
+                                                     loss_out=self._epoch_loss_pinned[:full]))
         if tail:
             losses.append(self.train_steps_from_host(self._host_x[full * B:], self._host_y[full * B:],
-                                                     1, tail))
+                                                     1, tail,
+                                                     loss_out=self._epoch_loss_pinned[full:full + 1]))
         torch.cuda.synchronize(self.device)
-        if self.comm is not None:
+        if self.persistent:
+            self.engine.check_errors()
+        elif self.comm is not None:
             self.comm.check_errors()
         epoch_loss = 0.0
         flat = torch.cat(losses).tolist() if losses else []
@@ -228,7 +238,7 @@ class Trainer:
         full = n // B
         tail = n - full * B
         eng.begin_epoch()
-        use_graph = c.cuda_graph
+        use_graph = c.cuda_graph and not self.persistent
         g_full = self._graph_for(B, data) if (use_graph and full > 0) else None
         g_multi = self._graph_for(B, data, self.UNROLL) if (use_graph and full >= self.UNROLL) else None
         epoch_loss = 0.0
@@ -261,7 +271,12 @@ class Trainer:
         chunk = min(eng.ring - self.UNROLL, max(li, 256))
         bi = 0
         while bi < full:
-            if g_multi is not None and full - bi >= self.UNROLL:
+            if self.persistent:
+                # one launch runs every step up to the next loss flush
+                adv = min(full - bi, chunk - pending)
+                eng.run_steps(data.images, data.labels, X_U8_GATHER, gidx=self._perm_dev, batch=B,
+                              nsteps=adv, idx_stride=B)
+            elif g_multi is not None and full - bi >= self.UNROLL:
                 g_multi.replay()
                 adv = self.UNROLL
             elif g_full is not None:
@@ -286,7 +301,9 @@ class Trainer:
         if not self.distributed_style and c.checkpoint_every_log:
             self.save()
         self.examples_seen += n
-        if self.comm is not None:
+        if self.persistent:
+            eng.check_errors()
+        elif self.comm is not None:
             self.comm.check_errors()
         return epoch_loss
 
@@ -418,6 +435,10 @@ class Trainer:
             if buf is None or buf.numel() < steps:
                 buf = self._loss_pinned = torch.empty(max(steps, 1024), dtype=torch.float32).pin_memory()
             loss_out = buf[:steps]
+        if self.persistent and self.native_runner:
+            # ONE persistent launch for the whole call; the copy stream feeds it step by step
+            eng.feeder(batch, hx.dtype).run(hx, hy, steps, loss_out)
+            return loss_out
         if self.cfg.cuda_graph and self.native_runner:
             # native loop (csrc/runner.cu): per-step copies, 16-step kernel graphs, no Python
             key = ("runner", batch, hx.dtype)

@@ -218,6 +218,31 @@ int b200_runner_destroy(void* h);
 int b200_pdl_enabled(void);
 int b200_net_set_phase_debug(long long* buf);
 
+/* ---- persistent step kernel (csrc/net_persist.cu) -------------------------------------- */
+/* `nsteps` optimizer steps of the MNIST net in ONE cooperative launch: worker CTAs run
+ * forward/backward, service CTAs form the fc gradients, sum the conv partial rows, exchange
+ * each bucket with the peers while backward still runs, apply SGD-momentum and publish the new
+ * weights. Ref: the loop body of src/train_dist.py:78-89 and DDP's overlapped all-reduce
+ * (src/train_dist.py:63,83). The argument block mirrors ops/persist.py:_PersistHost. */
+struct B200PersistHost;
+int b200_net_persist_host_size(void);
+/* out9 = {grid, workers, split, rows, images per worker, service CTAs, conv2 CTAs, W3 CTAs,
+ * W3 columns per CTA} for a per-GPU batch of B (host-only). */
+int b200_net_persist_plan(int B, int* out9);
+long long b200_net_persist_scratch_floats(int B);
+int b200_net_persist_smem_bytes(void);
+long long b200_net_persist_dbg_words(int* steps, int* phases);   /* phase-stamp buffer (debug) */
+int b200_net_persist_run(const struct B200PersistHost* args, void* stream);
+/* Host feeder: batches from pinned host memory into a device ring on a copy stream, one 32-bit
+ * stream write per step tells the running kernel what has landed; the kernel stores each
+ * step's loss into the caller's pinned buffer. Ref: DataLoader(pin_memory=True) + loss.item(),
+ * src/train_dist.py:40-45,85. */
+int b200_feeder_create(const struct B200PersistHost* tmpl, int ring_slots, void** out);
+int b200_feeder_run(void* h, const void* hx, const long long* hy, int steps, float* hloss,
+                    void* caller_stream);
+long long b200_feeder_launches(void* h);
+int b200_feeder_destroy(void* h);
+
 /* ---- bucket planner + reducer core (host only) --------------------------------------- */
 /* Ref: torch DDP's bucket rule reached from src/train_dist.py:63 */
 int b200_plan_buckets(const long long* bytes, int n, long long first_cap, long long cap,

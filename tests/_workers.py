@@ -170,7 +170,7 @@ def net_ddp_fused(rank, world, backend, out_dir, use_graph):
         y = torch.randint(0, 10, (B,), generator=g)
         a, b = oracle.make_masks(B, g)
         sx.copy_(x); sy.copy_(y); m2.copy_(a); m3.copy_(b)
-        if use_graph:
+        if use_graph is True:
             if graph is None:
                 s = torch.cuda.Stream()
                 s.wait_stream(torch.cuda.current_stream())
@@ -185,14 +185,57 @@ def net_ddp_fused(rank, world, backend, out_dir, use_graph):
                 with torch.cuda.graph(graph, stream=s):
                     eng.step(sx, sy, masks=(m2, m3))
             graph.replay()
+        elif use_graph == "persist":
+            # the persistent kernel, one step per launch so the oracle's masks can be injected
+            eng.run_steps(sx.view(B, 784), sy, 0, batch=B, nsteps=1, masks=(m2, m3), write_grad=True)
+            grads.append(eng.flat.grad.clone().cpu())
         else:
             eng.step(sx, sy, masks=(m2, m3), write_grad=True)
             grads.append(eng.flat.grad.clone().cpu())
     torch.cuda.synchronize()
     comm.check_errors()
+    if use_graph == "persist":
+        eng.check_errors()
     torch.save({"init": init, "final": eng.flat.param.clone().cpu(), "grads": grads,
                 "losses": eng.last_losses(steps), "steps": eng.steps_done()},
                os.path.join(out_dir, f"net_{rank}.pt"))
+    P.destroy_process_group()
+
+
+def net_ddp_persist_multi(rank, world, backend, out_dir):
+    """24 optimizer steps in ONE persistent launch per rank (Philox dropout, device-resident
+    shard), then the same 24 steps through the two-kernel step from the same start."""
+    import importlib
+    P = _pg()
+    DP = importlib.import_module(PKG + ".parallel.data_parallel").DataParallel
+    Net = importlib.import_module(PKG + ".models").Net
+    comm = P.init_process_group(backend=backend, rank=rank, world_size=world)
+    dev = comm.device
+    B, steps = 64, 24
+    g = torch.Generator().manual_seed(77 + rank)
+    data = torch.randint(0, 256, (B * steps, 784), dtype=torch.uint8, generator=g).to(dev)
+    labels = torch.randint(0, 10, (B * steps,), generator=g).to(dev)
+    perm = torch.randperm(B * steps, generator=g).to(torch.int32).to(dev)
+    out = {}
+    for mode in ("persistent", "two-kernel"):
+        torch.manual_seed(1 + rank)
+        ddp = DP(Net().to(dev), comm)
+        eng = ddp.fused_engine(lr=0.02, momentum=0.5, seed=3)
+        eng.begin_epoch()
+        if mode == "persistent":
+            eng.run_steps(data, labels, 2, gidx=perm, batch=B, nsteps=10, idx_stride=B)
+            eng.run_steps(data, labels, 2, gidx=perm, batch=B, nsteps=14, idx_stride=B)
+        else:
+            for _ in range(steps):
+                eng.step(data, labels, 2, gidx=perm, batch=B, idx_stride=B)
+        torch.cuda.synchronize()
+        comm.check_errors()
+        eng.check_errors()
+        out[mode] = {"final": eng.flat.param.clone().cpu(), "mom": eng.flat.momentum.clone().cpu(),
+                     "losses": eng.last_losses(steps), "steps": eng.steps_done(),
+                     "launches": eng.launches}
+        comm.host_barrier()
+    torch.save(out, os.path.join(out_dir, f"netp_{rank}.pt"))
     P.destroy_process_group()
 
 

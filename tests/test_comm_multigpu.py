@@ -38,13 +38,31 @@ def test_ddp_generic_peer(native_lib, tmp_path, fuse, algo):
     check_ddp_generic(res, world)
 
 
-@pytest.mark.parametrize("use_graph", [False, True])
+@pytest.mark.parametrize("use_graph", [False, True, "persist"])
 def test_net_ddp_fused_peer(native_lib, tmp_path, use_graph):
+    """Gradients == mean of the per-rank oracle gradients, parameters == oracle SGD, replicas
+    bit-identical: two-kernel step (eager, graph) and the persistent kernel."""
     from tests._ddp_checks import check_net_ddp
     world = _world()
     launch(_workers.net_ddp_fused, world, args=("b200", str(tmp_path), use_graph), timeout=600)
     res = [torch.load(tmp_path / f"net_{r}.pt") for r in range(world)]
-    check_net_ddp(res, world, check_grads=not use_graph)
+    check_net_ddp(res, world, check_grads=use_graph is not True)
+
+
+def test_net_ddp_persistent_multistep_peer(native_lib, tmp_path):
+    """24 steps per rank in two persistent launches: replicas bit-identical, momentum too, and
+    the trajectory follows the two-kernel step (different summation order only)."""
+    world = _world()
+    launch(_workers.net_ddp_persist_multi, world, args=("b200", str(tmp_path)), timeout=600)
+    res = [torch.load(tmp_path / f"netp_{r}.pt") for r in range(world)]
+    for r in range(world):
+        p, k = res[r]["persistent"], res[r]["two-kernel"]
+        assert p["steps"] == k["steps"] == 24 and p["launches"] == 2
+        assert torch.equal(p["final"], res[0]["persistent"]["final"])
+        assert torch.equal(p["mom"], res[0]["persistent"]["mom"])
+        torch.testing.assert_close(p["losses"], k["losses"], rtol=2e-4, atol=2e-5)
+        torch.testing.assert_close(p["final"], k["final"], rtol=2e-3, atol=2e-5)
+        assert (p["losses"] > 1.5).all() and (p["losses"] < 3.5).all()
 
 
 @pytest.mark.parametrize("algo", ["oneshot", "twoshot", "nvls"])

@@ -244,8 +244,13 @@ def test_native_runner_matches_python_loop(cuda_device):
     for native in (True, False):
         tr = Trainer(TrainConfig(learning_rate=0.02), distributed_style=True)
         tr.native_runner = native
+        tr.persistent = False     # this test pins the graph runner; tests/test_persist_gpu.py has the feeder
         l1 = tr.train_steps_from_host(hx, hy, 12, B)                     # per-step path only
+        torch.cuda.synchronize()
+        l1 = l1.clone()            # the trainer reuses one pinned loss buffer between calls
         l2 = tr.train_steps_from_host(hx[12 * B:], hy[12 * B:], 41, B)   # 2 chunks + 9 single steps
+        torch.cuda.synchronize()
+        l2 = l2.clone()
         l3 = tr.train_steps_from_host(hx[53 * B:], hy[53 * B:], 7, B)    # slots wrap after chunks
         torch.cuda.synchronize()
         if native:
