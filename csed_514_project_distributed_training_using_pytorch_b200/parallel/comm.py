@@ -260,11 +260,15 @@ class PeerComm(BaseComm):
     def check_errors(self):
         """Raise if a kernel's bounded wait on a peer timed out (host sync)."""
         e = self.err.cpu().tolist()
+        if e[0] == 2:    # the persistent step kernel gave up on one of its own counters
+            raise CommError(f"rank {self.rank}: persistent step kernel aborted, internal wait "
+                            f"#{e[2]} timed out (sequence {e[3] & 0xffffffff})")
         if e[0] != 0:
             where = {1: "barrier", 2: "broadcast(root waits)", 3: "broadcast(wait root)",
                      4: "send(wait ack)", 5: "recv", 6: "net all-reduce", 7: "one-shot all-reduce",
                      8: "two-shot reduce-scatter", 9: "two-shot all-gather",
-                     10: "NVLS all-reduce (inputs ready)", 11: "NVLS all-reduce (results)"
+                     10: "NVLS all-reduce (inputs ready)", 11: "NVLS all-reduce (results)",
+                     12: "persistent step kernel (gradient exchange)"
                      }.get(e[2], str(e[2]))
             raise CommError(f"rank {self.rank}: timed out waiting for rank {e[1]} in {where} "
                             f"(sequence {e[3] & 0xffffffff})")

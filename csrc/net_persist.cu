@@ -208,7 +208,9 @@ __device__ __forceinline__ bool wait_ge(const unsigned* p, unsigned target, cons
       if ((int)(v - target) >= 0) return true;
     }
     if (ld_volatile_u32(a.ctl + C_ABORT * CTL_STRIDE) != 0u) return false;
-    if (globaltimer_ns() - t0 > a.timeout_ns) {
+    // local waits get twice the peer timeout: when a peer is missing, the wait that names it
+    // (the gradient exchange) must be the one that fires first
+    if (globaltimer_ns() - t0 > 2ull * a.timeout_ns) {
       set_abort(a, where, 0xffffu, target);
       return false;
     }
@@ -610,7 +612,7 @@ __device__ __forceinline__ void worker_loop(const PersistArgs& a, float* smem) {
             if (v.y == want && v.w == want) break;
             if ((polls & 255u) == 0u) {
               if (ld_volatile_u32(ctl + C_ABORT * CTL_STRIDE) != 0u) break;
-              if (globaltimer_ns() - t0 > a.timeout_ns) { set_abort(a, 20u, 0xffffu, want); break; }
+              if (globaltimer_ns() - t0 > 2ull * a.timeout_ns) { set_abort(a, 20u, 0xffffu, want); break; }
             }
           }
         }
@@ -953,7 +955,7 @@ __device__ __forceinline__ void service_conv1(const PersistArgs& a, float* smem,
           if (pending && (++polls & 127u) == 0u) {
             if (t0 == 0) t0 = globaltimer_ns();
             if (ld_volatile_u32(ctl + C_ABORT * CTL_STRIDE) != 0u) { ok = false; break; }
-            if (globaltimer_ns() - t0 > a.timeout_ns) { set_abort(a, 30u, 0xffffu, tag); ok = false; break; }
+            if (globaltimer_ns() - t0 > 2ull * a.timeout_ns) { set_abort(a, 30u, 0xffffu, tag); ok = false; break; }
           }
         }
 #pragma unroll

@@ -239,6 +239,96 @@ def net_ddp_persist_multi(rank, world, backend, out_dir):
     P.destroy_process_group()
 
 
+def late_rank(rank, world, backend, out_dir, what):
+    """Failure detection: the last rank stays away from a collective for longer than
+    the communicator's timeout. Every other rank's kernel must give up, and the host must get an
+    exception that names the missing rank; tear-down must not hang."""
+    import importlib
+    import time
+    os.environ["B200DP_COMM_TIMEOUT_S"] = "1.0"
+    P = _pg()
+    comm = P.init_process_group(backend=backend, rank=rank, world_size=world)
+    CommError = importlib.import_module(PKG + ".parallel.comm").CommError
+    NativeError = importlib.import_module(PKG + "._native").NativeError
+    dev = comm.device
+    late = world - 1
+    err = None
+    x = comm.alloc(4096) if what == "twoshot" else torch.zeros(4096, device=dev)
+    x.fill_(float(rank + 1))
+    eng = None
+    if what == "persist":
+        DP = importlib.import_module(PKG + ".parallel.data_parallel").DataParallel
+        Net = importlib.import_module(PKG + ".models").Net
+        torch.manual_seed(1)
+        eng = DP(Net().to(dev), comm).fused_engine(lr=0.02, momentum=0.5)
+        bx = torch.randn(4 * 16, 784, device=dev)
+        by = torch.randint(0, 10, (4 * 16,), device=dev)
+    comm.all_reduce(x.clone(), op="sum", algo="oneshot")       # everyone healthy: no error
+    torch.cuda.synchronize()
+    comm.check_errors()
+    comm.host_barrier()
+    t0 = time.time()
+    if rank == late:
+        time.sleep(3.5)                                        # > timeout: the others give up
+    try:
+        if what == "persist":
+            eng.run_steps(bx, by, 0, batch=16, nsteps=4)
+            torch.cuda.synchronize()
+            eng.check_errors()
+        else:
+            comm.all_reduce(x, op="sum", algo=what)
+            torch.cuda.synchronize()
+            comm.check_errors()
+    except (CommError, NativeError) as e:
+        err = str(e)
+    waited = time.time() - t0
+    torch.save({"err": err, "waited": waited}, os.path.join(out_dir, f"late_{rank}.pt"))
+    P.destroy_process_group()
+
+
+def protocol_stress(rank, world, backend, out_dir, iters):
+    """Randomised arrival order on every collective (stands in for racecheck, which is closed on
+    this pool): before each call every rank burns a random number of device cycles, so each
+    protocol sees every interleaving of early and late peers; values are small integers, so
+    every sum is exact and any torn, stale or missing word shows."""
+    P = _pg()
+    comm = P.init_process_group(backend=backend, rank=rank, world_size=world)
+    dev = comm.device
+    rng = torch.Generator().manual_seed(4242 + 17 * rank)
+    sizes = [64, 4096, 1 << 16, 3 << 18]                     # floats: tagged, tagged, bulk, bulk
+    bufs = {n: comm.alloc(n) for n in sizes}
+    bad = []
+    for it in range(iters):
+        n = sizes[it % len(sizes)]
+        algo = ("oneshot", "twoshot")[(it // len(sizes)) % 2]
+        if algo == "oneshot" and n > (1 << 16):
+            algo = "twoshot"
+        delay = int(torch.randint(0, 400000, (1,), generator=rng))   # up to ~0.2 ms of spin
+        torch.cuda._sleep(delay)
+        x = bufs[n]
+        x.copy_(torch.arange(n, device=dev, dtype=torch.float32).remainder_(97).add_(rank * 3 + it % 5))
+        comm.all_reduce(x, op="sum", algo=algo)
+        want = (torch.arange(n, device=dev, dtype=torch.float32).remainder_(97) * world
+                + 3 * (world * (world - 1) // 2) + world * (it % 5))
+        if not torch.equal(x, want):
+            bad.append((it, algo, n, int((x != want).sum())))
+        if it % 7 == 3:
+            torch.cuda._sleep(int(torch.randint(0, 200000, (1,), generator=rng)))
+            comm.barrier()
+        if it % 11 == 5:
+            root = it % world
+            b = bufs[64]
+            b.fill_(float(100 * rank + it))
+            torch.cuda._sleep(int(torch.randint(0, 200000, (1,), generator=rng)))
+            comm.broadcast(b, root=root)
+            if not torch.equal(b, torch.full_like(b, float(100 * root + it))):
+                bad.append((it, "broadcast", 64, -1))
+    torch.cuda.synchronize()
+    comm.check_errors()
+    torch.save({"bad": bad, "iters": iters}, os.path.join(out_dir, f"stress_{rank}.pt"))
+    P.destroy_process_group()
+
+
 def mlp_ddp(rank, world, backend, out_dir, algo):
     """bf16 MLP on tcgen05 GEMMs under DataParallel: per-layer buckets, fused all-reduce +
     sharded master-weight SGD, overlap with backward."""
@@ -263,8 +353,11 @@ def mlp_ddp(rank, world, backend, out_dir, algo):
     torch.cuda.current_stream().wait_stream(ddp.reducer.stream)
     torch.cuda.synchronize()
     comm.check_errors()
+    # fp32 master weights: whole buckets (one-shot) or this rank's shard of each (two-shot, NVLS)
+    master = [(m.float().cpu(), int(base), int(lo), int(hi))
+              for (m, _mom, base), (lo, hi) in zip(ddp.reducer.state, ddp.reducer.ranges)]
     torch.save({"init": init, "final": ddp.flat.param.clone().float().cpu(),
-                "losses": [l.item() for l in losses],
+                "losses": [l.item() for l in losses], "master": master,
                 "order": ddp.reducer.core.completion_order()},
                os.path.join(out_dir, f"mlp_{rank}.pt"))
     P.destroy_process_group()

@@ -77,41 +77,63 @@ def test_mlp_ddp_peer(native_lib, tmp_path, algo):
         assert torch.equal(res[r]["init"], res[0]["init"])
         assert torch.equal(res[r]["final"], res[0]["final"])
         assert res[r]["order"] == [0, 1, 2]          # buckets complete back-to-front
-    # fp32 oracle of the same schedule (mean of per-rank gradients, SGD-momentum)
+    # fp32 master weights, reassembled from the ranks' shards
+    got_master = res[0]["init"].clone()
+    for r in range(world):
+        for m, base, lo, hi in res[r]["master"]:
+            n = min(m.numel(), hi - lo - base)
+            if n > 0:
+                got_master[lo + base:lo + base + n] = m[:n]
+    # Oracle of the same schedule that rounds where the device rounds: bf16 weights from the
+    # fp32 master, bf16 hidden activations, bf16 dlogits / dx / dW / db, fp32 accumulation of
+    # the ranks' bf16 gradients, SGD-momentum on the fp32 master.
+    bf = lambda t: t.to(torch.bfloat16).float()
     torch.manual_seed(50)
     model = WideMLP((784, 256, 128, 10))
     flat = FlatParams(model, with_momentum=False)
     master = flat.param.float().clone()
     assert torch.equal(master, res[0]["init"])
-    views = flat.views(master)
-    ps = [v.clone().requires_grad_(True) for v in views]
+    ps = [v.clone() for v in flat.views(master)]
     bufs = [torch.zeros_like(p) for p in ps]
+    B = 32
     for step in range(6):
         gs = [torch.zeros_like(p) for p in ps]
+        Wq = [bf(p) for p in ps]
         for r in range(world):
             g = torch.Generator().manual_seed(1000 * step + r)
-            x = torch.randn(32, 784, generator=g).to(torch.bfloat16).float()
-            y = torch.randint(0, 10, (32,), generator=g)
-            h = x
-            for i in range(3):
-                h = h @ ps[2 * i].to(torch.bfloat16).float().t() + ps[2 * i + 1].to(torch.bfloat16).float()
-                if i < 2:
-                    h = torch.relu(h)
-            for p in ps:
-                p.grad = None
-            torch.nn.functional.cross_entropy(h, y).backward()
-            for a, p in zip(gs, ps):
-                a += p.grad
-        with torch.no_grad():
-            for p, a, b in zip(ps, gs, bufs):
-                b.mul_(0.5).add_(a / world)
-                p.sub_(0.1 * b)
+            x = bf(torch.randn(B, 784, generator=g))
+            y = torch.randint(0, 10, (B,), generator=g)
+            h0 = x
+            h1 = bf(torch.relu(h0 @ Wq[0].t() + Wq[1]))
+            h2 = bf(torch.relu(h1 @ Wq[2].t() + Wq[3]))
+            logits = h2 @ Wq[4].t() + Wq[5]
+            d3 = torch.softmax(logits, 1)
+            d3[torch.arange(B), y] -= 1.0
+            d3 = bf(d3 / B)
+            d2 = bf((d3 @ Wq[4]) * (h2 > 0))
+            d1 = bf((d2 @ Wq[2]) * (h1 > 0))
+            for i, (d, h) in enumerate(((d1, h0), (d2, h1), (d3, h2))):
+                gs[2 * i] += bf(d.t() @ h)
+                gs[2 * i + 1] += bf(d.sum(0))
+        for p, a, b in zip(ps, gs, bufs):
+            b.mul_(0.5).add_(a / world)
+            p.sub_(0.1 * b)
+    errs = {}
     for s, p in zip(flat.slots, ps):
-        got = res[0]["final"][s.offset:s.offset + s.numel].view(s.shape)
-        delta_ref = p.detach() - res[0]["init"][s.offset:s.offset + s.numel].view(s.shape)
-        delta_got = got - res[0]["init"][s.offset:s.offset + s.numel].view(s.shape)
-        err = (delta_got - delta_ref).norm() / (delta_ref.norm() + 1e-12)
-        assert err < 0.3, f"update mismatch {err:.3f} for {s.name}"
+        init = res[0]["init"][s.offset:s.offset + s.numel].view(s.shape)
+        delta_ref = p - init
+        delta_got = got_master[s.offset:s.offset + s.numel].view(s.shape) - init
+        errs[s.name] = float((delta_got - delta_ref).norm() / (delta_ref.norm() + 1e-12))
+        # the bf16 replica is the fp32 master rounded once
+        torch.testing.assert_close(res[0]["final"][s.offset:s.offset + s.numel].view(s.shape),
+                                   bf(got_master[s.offset:s.offset + s.numel].view(s.shape)),
+                                   rtol=0, atol=0)
+    print("mlp update errors vs the rounding oracle:", {k: round(v, 4) for k, v in errs.items()})
+    # what is left is summation order inside the GEMMs and the all-reduce (fp32 accumulation)
+    # and the occasional bf16 rounding flip it causes: a sign error or a dropped rank in any
+    # one tensor would show as an error of order 1
+    for name, err in errs.items():
+        assert err < 0.03, f"update mismatch {err:.4f} for {name}: {errs}"
 
 
 @pytest.mark.parametrize("kind,bn", [("cta", 128), ("persistent", 256), ("persistent", 128)])
@@ -124,6 +146,32 @@ def test_gemm_reduce_scatter_peer(native_lib, tmp_path, kind, bn):
     for r in range(world):
         assert torch.equal(res[r]["got"], res[0]["got"])
         torch.testing.assert_close(res[r]["got"], want, rtol=1.6e-2, atol=0.3)
+
+
+@pytest.mark.parametrize("what", ["oneshot", "twoshot", "persist"])
+def test_late_rank_is_named(native_lib, tmp_path, what):
+    """SURVEY §5 failure detection (reference site: src/train_dist.py:146 runs with library
+    defaults and would hang): a rank that stays away longer than the timeout surfaces on every
+    other rank as an exception naming it, after about the timeout, and the group tears down."""
+    world = _world()
+    launch(_workers.late_rank, world, args=("b200", str(tmp_path), what), timeout=300)
+    res = [torch.load(tmp_path / f"late_{r}.pt") for r in range(world)]
+    late = world - 1
+    for r in range(world - 1):
+        assert res[r]["err"] is not None, f"rank {r} did not notice the missing rank"
+        assert f"rank {late}" in res[r]["err"] or f"peer {late}" in res[r]["err"], res[r]["err"]
+        assert "timed out" in res[r]["err"]
+        assert 0.9 < res[r]["waited"] < 3.4, res[r]["waited"]      # gave up at the timeout, not at the sleep
+
+
+def test_protocols_under_random_delays(native_lib, tmp_path):
+    """Tagged-word and flag protocols with every rank arriving at a random time, 240 collectives
+    in a row on the same staging buffers (double-buffer reuse, sequence wrap of the slot bit)."""
+    world = _world()
+    launch(_workers.protocol_stress, world, args=("b200", str(tmp_path), 240), timeout=600)
+    res = [torch.load(tmp_path / f"stress_{r}.pt") for r in range(world)]
+    for r in range(world):
+        assert res[r]["iters"] == 240 and res[r]["bad"] == [], res[r]["bad"][:5]
 
 
 def test_trainer_distributed_peer(native_lib, tmp_path):
