@@ -50,7 +50,9 @@ class _PersistHost(C.Structure):   # mirrors B200PersistHost in csrc/net_persist
                 ("seq_ctr", c_p),
                 ("err", c_p),
                 ("timeout_ns", c_ull),
-                ("dbg", c_p)]
+                ("dbg", c_p),
+                ("label_slots", c_i), ("label_pos", c_u),
+                ("epoch_begin", c_i), ("pad1", c_i)]
 
 
 N.register_sigs({
@@ -87,6 +89,7 @@ class PersistentNetEngine(FusedNetEngine):
         self._pscratch = {}
         self._perr = torch.zeros(4, dtype=torch.int32, device=self.device)
         self._feeders = {}
+        self._hcache = {}
         self._dbg = None
         if self.comm is not None and self.comm.world_size > 1:
             self.comm.net_channel()      # staging + sequence counter shared with kernel B
@@ -124,7 +127,8 @@ class PersistentNetEngine(FusedNetEngine):
 
     # ------------------------------------------------------------------ steps
     def run_steps(self, x, y, x_mode=X_F32, gidx=None, batch=None, nsteps: int = 1,
-                  idx_stride: int = 0, masks=None, write_grad: bool = False, update: bool = True):
+                  idx_stride: int = 0, masks=None, write_grad: bool = False, update: bool = True,
+                  begin_epoch: bool = False):
         """`nsteps` optimizer steps on the current stream, one launch, no host sync.
 
         Gather modes (X_U8_GATHER / X_F32_GATHER): x, y are the device-resident dataset and
@@ -133,14 +137,22 @@ class PersistentNetEngine(FusedNetEngine):
         Direct modes (X_F32 / X_U8): x is [nsteps * batch, 784], y [nsteps * batch]; step s
         reads rows [s * batch, (s + 1) * batch).
         write_grad: the averaged gradient of the last step goes to `flat.grad`;
-        update=False leaves parameters and momentum untouched (nsteps must be 1)."""
+        update=False leaves parameters and momentum untouched (nsteps must be 1);
+        begin_epoch=True marks the first of these steps as the start of an epoch inside the
+        launch (same effect as calling `begin_epoch()` first, without the extra device op)."""
         gather = x_mode in (X_U8_GATHER, X_F32_GATHER)
         if batch is None:
             batch = (gidx.shape[0] if gather else x.shape[0] // max(1, nsteps))
         B = int(batch)
         if not update and nsteps != 1:
             raise N.NativeError("update=False only makes sense for a single step")
-        h = self._host_args(B, x_mode, self._mask_mode(masks))
+        mm = self._mask_mode(masks)
+        key = (B, x_mode, mm, self._dbg is None)
+        h = self._hcache.get(key)            # the argument block is built once per shape
+        if h is None:
+            h = self._hcache[key] = self._host_args(B, x_mode, mm)
+        h.epoch_begin = 1 if begin_epoch else 0
+        h.m2buf = h.m3buf = None
         h.x, h.labels, h.gidx = N.ptr(x), N.ptr(y), N.ptr(gidx)
         h.nsteps, h.update = int(nsteps), 1 if update else 0
         h.grad_out = self.flat.grad.data_ptr() if write_grad else None
@@ -157,6 +169,7 @@ class PersistentNetEngine(FusedNetEngine):
         """Debug aid: per-CTA, per-step clock64/globaltimer stamps of the persistent kernel's
         phases (scripts/persist_phases.py turns them into a timeline). Returns the buffer
         viewed as [148, steps, phases, 2] int64."""
+        self._hcache = {}
         if not on:
             self._dbg = None
             return None

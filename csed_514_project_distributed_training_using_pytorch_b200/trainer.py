@@ -237,7 +237,9 @@ class Trainer:
         n_batches = len(batches)
         full = n // B
         tail = n - full * B
-        eng.begin_epoch()
+        if not self.persistent:
+            eng.begin_epoch()
+        epoch_open = False
         use_graph = c.cuda_graph and not self.persistent
         g_full = self._graph_for(B, data) if (use_graph and full > 0) else None
         g_multi = self._graph_for(B, data, self.UNROLL) if (use_graph and full >= self.UNROLL) else None
@@ -275,7 +277,8 @@ class Trainer:
                 # one launch runs every step up to the next loss flush
                 adv = min(full - bi, chunk - pending)
                 eng.run_steps(data.images, data.labels, X_U8_GATHER, gidx=self._perm_dev, batch=B,
-                              nsteps=adv, idx_stride=B)
+                              nsteps=adv, idx_stride=B, begin_epoch=not epoch_open)
+                epoch_open = True
             elif g_multi is not None and full - bi >= self.UNROLL:
                 g_multi.replay()
                 adv = self.UNROLL
@@ -294,8 +297,12 @@ class Trainer:
                     self.save()
         if tail:
             # the short last batch (60000 % 64 = 32): own launch, indices at an explicit offset
-            eng.step(data.images, data.labels, X_U8_GATHER, gidx=self._perm_dev[full * B:],
-                     batch=tail)
+            if self.persistent:
+                eng.run_steps(data.images, data.labels, X_U8_GATHER, gidx=self._perm_dev[full * B:],
+                              batch=tail, nsteps=1)
+            else:
+                eng.step(data.images, data.labels, X_U8_GATHER, gidx=self._perm_dev[full * B:],
+                         batch=tail)
             pending += 1
         flush(n_batches)
         if not self.distributed_style and c.checkpoint_every_log:

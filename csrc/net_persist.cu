@@ -73,7 +73,7 @@ static_assert(OFF_W2 % 4 == 0 && P2_ROW % 4 == 0 && OFF_W3 % 4 == 0 && FC_SMALL_
                   FC_SMALL_N % 4 == 0, "groups must be float4 aligned");
 
 // control words, one per 128-byte line
-enum { C_ACT = 0, C_P2, C_DFC, C_D2, C_ABORT, C_STARTED, C_NWORDS };
+enum { C_ACT = 0, C_P2, C_DFC, C_ABORT, C_STARTED, C_NWORDS };
 constexpr int CTL_STRIDE = 32;   // u32 words between counters
 
 struct PersistArgs {
@@ -89,17 +89,22 @@ struct PersistArgs {
   int nsteps;
   int update;                // 0: leave params/momentum alone (gradient-only run)
   int n_workers, split, rows, ipc;   // ipc = images per worker per step
-  int n_service, n2, n3, kw;         // conv2 CTAs, W3 CTAs, W3 columns per CTA
+  int n_service, n3, kw;             // service CTAs, of which W3 CTAs; W3 columns per CTA
   int idx_stride, n_idx;
   int ring_slots;            // direct modes: slot of local step ls is (ring_pos + ls) % ring_slots
   unsigned ring_pos;
-  const unsigned* feed_ready;   // null, or: step (feed_base + ls) is in its slot once *feed_ready > feed_base + ls
+  const unsigned* feed_ready;   // null, or: global step g = feed_base + ls is in its slot once
+                                // feed_ready[32 * (g & 1)] > g (two copy streams, one word each)
   unsigned* feed_consumed;
   unsigned feed_base;
+  int label_slots;           // labels of local step ls: labels + ((label_pos + ls) % label_slots) * B
+  unsigned label_pos;
+  int epoch_begin;           // 1: this launch starts an epoch (step_ctr[1] := step_ctr[0])
   float* acts;
   float* part2;
   uint2* part1;              // [rows][260] {value, tag}: conv1 partial rows
   uint2* w1box;              // [260] {value, tag}: conv1's updated weights, service -> workers
+  uint2* w2box;              // [5020] {value, tag}: conv2's updated weights, worker slices -> all workers
   unsigned tag_base;         // (launch id << 16): tag of local step ls is tag_base | (ls + 1)
   unsigned* ctl;
   float* loss_ring;
@@ -457,276 +462,7 @@ __device__ __forceinline__ float normalize_px(unsigned v) {
 }
 
 // =========================================================================================
-// WORKER
-// =========================================================================================
-template <bool SPLIT>
-__device__ __forceinline__ void worker_loop(const PersistArgs& a, float* smem) {
-  const WorkerSmem w = carve_worker(smem);
-  const int t = threadIdx.x;
-  const int role = SPLIT ? (int)(blockIdx.x & 1) : 2;
-  const int slot = SPLIT ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
-  const int nslots = SPLIT ? a.n_workers >> 1 : a.n_workers;
-  // the halves of the backward this CTA owns
-  const int co0 = SPLIT ? role * 10 : 0, nco = SPLIT ? 10 : C2;
-  const int ci0 = SPLIT ? role * 5 : 0, nci = SPLIT ? 5 : C1;
-  unsigned* ctl = a.ctl;
-
-  if (t == 0) {
-    for (int i = 1; i < 5; ++i) mbar_init(w.bar + i, 1);   // [1] conv2, [2] fc, [3..4] images
-    fence_barrier_init();
-  }
-  const unsigned long long step0 = a.step_ctr[0];
-  const long long idx_base0 = (a.idx_stride != 0) ? (long long)(step0 - a.step_ctr[1]) * a.idx_stride : 0ll;
-  __syncthreads();
-  if (t == 0) red_release_gpu_add_u32(ctl + C_STARTED * CTL_STRIDE, 1u);
-
-  const int ipc = a.ipc;
-  const int nitems = a.nsteps * ipc;       // (step, image) work items of this CTA, in order
-  const size_t row_bytes = (a.x_mode == 0 || a.x_mode == 3) ? IMG_SZ * 4 : IMG_SZ;
-  const bool is_u8 = (a.x_mode == 1 || a.x_mode == 2);
-  const float inv_B = 1.0f / (float)a.B;
-  float* row2 = a.part2 + (size_t)slot * P2_ROW;
-  uint2* row1 = a.part1 + (size_t)slot * C1_PAIRS;
-
-  // Issue the bulk copy of item k's image (lane 0 of warp 0 only). Returns false if the
-  // item has no image (img >= B) or its data is not there yet and `block` is false.
-  int issued = 0;   // items whose image copy has been issued (thread 0's view)
-  auto item_img = [&](int k, int& ls, int& img) {
-    ls = k / ipc;
-    img = slot + (k - ls * ipc) * nslots;
-  };
-  auto issue_image = [&](int k, bool block) -> bool {
-    int ls, img;
-    item_img(k, ls, img);
-    unsigned long long* bar = w.bar + 3 + (k & 1);
-    if (img >= a.B) {            // ragged tail: nothing to fetch, complete the phase empty
-      mbar_arrive(bar);
-      return true;
-    }
-    if (a.feed_ready) {
-      const unsigned want = a.feed_base + (unsigned)ls + 1u;
-      if (block) {
-        if (!wait_ge(a.feed_ready, want, a, 20u, true)) { mbar_arrive(bar); return true; }
-      } else if ((int)(ld_acquire_sys_u32(a.feed_ready) - want) < 0) {
-        return false;
-      }
-    }
-    size_t r;
-    if (a.x_mode >= 2) r = (size_t)__ldg(a.gidx + idx_base0 + (long long)ls * a.idx_stride + img);
-    else r = (size_t)((a.ring_pos + (unsigned)ls) % (unsigned)a.ring_slots) * a.B + img;
-    const char* src = (const char*)a.x + r * row_bytes;
-    void* dst = is_u8 ? (void*)(w.xu + (k & 1) * 784) : (void*)(w.xs + (k & 1) * IMG_SZ);
-    fence_proxy_async();
-    mbar_expect_tx(bar, (unsigned)row_bytes);
-    bulk_g2s(dst, src, (unsigned)row_bytes, bar);
-    return true;
-  };
-
-  constexpr int FETCH_T = 288;   // lane 0 of warp 9
-  constexpr int SIGNAL_T = 300;  // a thread of warp 9 that the backward's wide phases leave idle
-  for (int k = 0; k < nitems; ++k) {
-    int ls, img;
-    item_img(k, ls, img);
-    const bool first_of_step = (k == ls * ipc);
-    const bool last_of_step = (k == ls * ipc + ipc - 1);
-    const bool have = img < a.B;
-    const unsigned long long step = step0 + (unsigned long long)ls;
-
-    // ---- fetch duties belong to ONE thread of warp 9, the warp conv1 leaves idle: it waits
-    // for a parameter group's update, then issues the bulk copy that completes on the
-    // group's mbarrier. conv1's group comes first (it is the last one published).
-    // (the conv2 and fc groups; conv1's 1 KB comes through the tagged mailbox below)
-    auto fetch_group = [&](int g, bool block) -> bool {   // 1 conv2, 2 fc
-      const unsigned* ctr = ctl + (g == 1 ? C_D2 : C_DFC) * CTL_STRIDE;
-      const unsigned per = g == 1 ? (unsigned)a.n2 : (unsigned)(a.n3 + 1);
-      const int lo = g == 1 ? OFF_W2 : OFF_W3;
-      const int hi = g == 1 ? OFF_W3 : FLAT_SZ;
-      const unsigned want = (unsigned)ls * per;
-      if (!block && (int)(ld_acquire_gpu_u32(ctr) - want) < 0) return false;
-      if (wait_ge(ctr, want, a, 21u + g)) {
-        fence_proxy_async();
-        mbar_expect_tx(w.bar + g, (unsigned)(hi - lo) * 4u);
-        bulk_g2s(w.P + lo, a.params + lo, (unsigned)(hi - lo) * 4u, w.bar + g);
-      } else {
-        mbar_arrive(w.bar + g);   // aborted: complete the phase so nobody hangs on it
-      }
-      return true;
-    };
-    if (t == FETCH_T && issued <= k) { issue_image(k, true); issued = k + 1; }
-
-    // dropout masks (Philox keyed by step and sample: replays and the two-kernel path agree)
-    PSTAMP(ls, 0);
-    int tgt = 0;
-    if (have) {
-      if (t >= 32 && t < 32 + C2) {
-        const int c = t - 32;
-        float m = 1.0f;
-        if (a.mask_mode == 1) m = dropout_mask_value(a.seed, step, a.sample_base + img, 0x20000u + c, 0.5f);
-        else if (a.mask_mode == 2) m = a.m2buf[(size_t)img * C2 + c];
-        w.m2s[c] = m;
-      } else if (t >= 64 && t < 64 + FC1) {
-        const int j = t - 64;
-        float m = 1.0f;
-        if (a.mask_mode == 1) m = dropout_mask_value(a.seed, step, a.sample_base + img, 0x30000u + j, 0.5f);
-        else if (a.mask_mode == 2) m = a.m3buf[(size_t)img * FC1 + j];
-        w.m3s[j] = m;
-      }
-    }
-    // ---- image
-    mbar_wait(w.bar + 3 + (k & 1), (unsigned)(k >> 1) & 1u);
-    if (have && t < 32) {
-      // the label is read only now: in host-fed mode the batch is known to have landed once
-      // the image copy completed (the fetch thread waited for the step's ready value)
-      size_t r;
-      if (a.x_mode >= 2) r = (size_t)__ldg(a.gidx + idx_base0 + (long long)ls * a.idx_stride + img);
-      else r = (size_t)((a.ring_pos + (unsigned)ls) % (unsigned)a.ring_slots) * a.B + img;
-      tgt = (int)__ldcg(a.labels + r);   // ring slots are rewritten while the kernel runs: not via L1
-    }
-    float* xs = w.xs + (k & 1) * IMG_SZ;
-    if (is_u8 && have) {
-      const uchar4* src = reinterpret_cast<const uchar4*>(w.xu + (k & 1) * 784);
-      if (t < IMG_SZ / 4) {
-        const uchar4 v = src[t];
-        reinterpret_cast<float4*>(xs)[t] =
-            make_float4(normalize_px(v.x), normalize_px(v.y), normalize_px(v.z), normalize_px(v.w));
-      }
-    }
-    // ---- conv1's weights: at the first step of a launch from global memory, afterwards from
-    // the mailbox the two conv1 service CTAs fill with {value, tag} pairs. Each of 130 threads
-    // polls its own 16-byte word: the data is the signal, one L2 round trip after it lands.
-    if (first_of_step && t < C1_HALF) {
-      const int e0 = 2 * t;                       // pairs e0, e0 + 1 (same half: 130 is even)
-      const int h = e0 / C1_HALF, i0 = e0 - h * C1_HALF;
-      float v0, v1;
-      if (ls == 0) {
-        v0 = __ldcg(a.params + c1_flat(h, i0));
-        v1 = __ldcg(a.params + c1_flat(h, i0 + 1));
-      } else {
-        const unsigned want = a.tag_base | (unsigned)ls;     // tag of local step ls - 1
-        const uint4* src = reinterpret_cast<const uint4*>(a.w1box) + t;
-        uint4 v = ld_volatile_u4(src);
-        if (!(v.y == want && v.w == want)) {
-          const unsigned long long t0 = globaltimer_ns();
-          for (unsigned polls = 1;; ++polls) {
-            v = ld_volatile_u4(src);
-            if (v.y == want && v.w == want) break;
-            if ((polls & 255u) == 0u) {
-              if (ld_volatile_u32(ctl + C_ABORT * CTL_STRIDE) != 0u) break;
-              if (globaltimer_ns() - t0 > 2ull * a.timeout_ns) { set_abort(a, 20u, 0xffffu, want); break; }
-            }
-          }
-        }
-        v0 = __uint_as_float(v.x);
-        v1 = __uint_as_float(v.z);
-      }
-      w.P[c1_flat(h, i0)] = v0;
-      w.P[c1_flat(h, i0 + 1)] = v1;
-    }
-    if (t == 0) w.flags[0] = (int)ld_volatile_u32(ctl + C_ABORT * CTL_STRIDE);
-    __syncthreads();
-    if (w.flags[0] != 0) break;     // uniform: one thread sampled the abort word
-    PSTAMP(ls, 1);
-    if (have) conv1_fwd_img(xs, w.P + OFF_W1, w.P + OFF_B1, w.a1s, w.pos1s);
-    bool fc_issued = !first_of_step;
-    if (t == FETCH_T) {
-      if (first_of_step) {
-        fetch_group(1, true);                    // conv2 is needed next
-        fc_issued = fetch_group(2, false);       // fc only if it is already there
-      }
-      // the other image buffer is free (its item has finished): fetch one item ahead
-      if (k + 1 < nitems && issued == k + 1 && issue_image(k + 1, false)) issued = k + 2;
-    }
-    if (first_of_step) mbar_wait(w.bar + 1, (unsigned)ls & 1u);
-    __syncthreads();
-    PSTAMP(ls, 2);
-    if (have) conv2_fwd_img(w.a1s, w.P + OFF_W2, w.P + OFF_B2, w.m2s, w.a2s, w.pos2s);
-    if (t == FETCH_T && !fc_issued) fetch_group(2, true);
-    if (first_of_step) mbar_wait(w.bar + 2, (unsigned)ls & 1u);
-    __syncthreads();
-    PSTAMP(ls, 3);
-    if (have) {
-      fc1_fwd_s(w.a2s, w.P + OFF_W3, w.P + OFF_B3, w.m3s, w.h1s);
-      __syncthreads();
-      PSTAMP(ls, 4);
-      fc2_fwd_img(w.h1s, w.P + OFF_W4, w.P + OFF_B4, w.logit);
-      __syncthreads();
-      float loss_img = 0.0f;
-      if (t < 32) {
-        // log_softmax + NLL + its gradient (src/model.py:22, src/train.py:74), one class per lane
-        const float z = (t < NCLS) ? w.logit[t] : -INFINITY;
-        const float mx = warp_max(z);
-        const float e = (t < NCLS) ? expf(z - mx) : 0.0f;
-        const float lse = mx + logf(warp_sum(e));
-        const float lp = z - lse;
-        if (t < NCLS) w.dlog[t] = (expf(lp) - (t == tgt ? 1.0f : 0.0f)) * inv_B;
-        loss_img = -__shfl_sync(0xffffffffu, lp, tgt) * inv_B;
-      }
-      __syncthreads();
-      PSTAMP(ls, 5);
-      fc2_bwd_img(w.dlog, w.h1s, w.m3s, w.P + OFF_W4, w.dpre, nullptr, nullptr, true, false);
-      __syncthreads();
-      // ---- publish this image's fc operands: the service CTAs form dW3, db3, dW4, db4
-      if (role != 1) {
-        float* act = a.acts + (size_t)img * ACT_STRIDE;
-        act[ACT_A2 + t] = w.a2s[t];                                  // NT == 320 == A2_SZ
-        if (t < FC1) { act[ACT_DPRE + t] = w.dpre[t]; act[ACT_H1 + t] = w.h1s[t]; }
-        if (t < NCLS) act[ACT_DLOG + t] = w.dlog[t];
-        if (t == 0) act[ACT_LOSS] = loss_img;
-      }
-      fc1_bwd_img<true>(w.dpre, w.a2s, w.m2s, w.P + OFF_W3, w.g2s, nullptr, nullptr, true, false);
-      __syncthreads();
-      PSTAMP(ls, 6);
-      build_conv2_dense(w.g2s, w.pos2s, w.m2s, w.Ds, w.live, w.slot_of);
-      __syncthreads();
-      PSTAMP(ls, 7);
-      // Signals are raised by a thread that has no work in the phase that follows (conv2's
-      // weight gradient uses threads 0..275): the CTA barrier above ordered every thread's
-      // stores before its fence, and the fence's wait for L2 acknowledgements costs nobody.
-      if (role != 1 && t == SIGNAL_T) { __threadfence(); signal_add(ctl + C_ACT * CTL_STRIDE); }
-      // conv2's weight gradient first: its reduction then hides behind dgrad + conv1 wgrad
-      if (SPLIT) {
-        conv2_wgrad_part<false>(w.g2s, w.pos2s, w.m2s, w.a1s, row2, row2 + W2_SZ, co0, nco, true);
-      } else {
-        conv2_wgrad_part<true>(w.g2s, w.pos2s, w.m2s, w.a1s, w.acc + OFF_W2, w.acc + OFF_B2, 0, C2,
-                               first_of_step);
-      }
-      PSTAMP(ls, 8);
-      if (SPLIT) __syncthreads();       // every thread's stores of the conv2 partial row are issued
-      if (SPLIT && t == SIGNAL_T) { __threadfence(); signal_add(ctl + C_P2 * CTL_STRIDE); }   // idle in the product
-      conv2_dgrad_T_part(w.Ds, w.live, w.live[C2], w.P + OFF_W2, w.Ts, ci0, nci);
-      __syncthreads();
-      PSTAMP(ls, 9);
-      conv2_dgrad_gather_part(w.Ts, w.a1s, w.g1s, ci0, nci);
-      __syncthreads();
-      PSTAMP(ls, 10);
-      if (SPLIT) {
-        conv1_wgrad_half(w.g1s, w.pos1s, xs, row1, role, a.tag_base | (unsigned)(ls + 1));
-        __syncthreads();                // xs / g1s are reused by the next item
-        PSTAMP(ls, 11);
-      } else {
-        conv1_wgrad_img(w.g1s, w.pos1s, xs, w.acc + OFF_W1, w.acc + OFF_B1, first_of_step);
-        __syncthreads();
-      }
-    }
-    if (!SPLIT && last_of_step) {
-      // several images per CTA: one partial row per step, written once
-      if (slot < a.B) {
-        for (int i = t; i < P2_ROW / 4; i += NT)
-          reinterpret_cast<float4*>(row2)[i] = reinterpret_cast<const float4*>(w.acc + OFF_W2)[i];
-        if (t < C1_PAIRS) {
-          const int h = t / C1_HALF, i = t - h * C1_HALF;
-          st_pair(row1 + t, w.acc[c1_flat(h, i)], a.tag_base | (unsigned)(ls + 1));
-        }
-        __threadfence();
-        __syncthreads();
-        if (t == 0) signal_add(ctl + C_P2 * CTL_STRIDE);
-      }
-    }
-  }
-}
-
-// =========================================================================================
-// SERVICE
+// Helpers shared by workers and service CTAs: tagged exchange, update, row sums, staging
 // =========================================================================================
 struct ServiceSmem {
   float4* gs;       // gradient slice in float4 units (<= 1024 items)
@@ -814,9 +550,13 @@ __device__ __forceinline__ bool ll_gather_sum(const PersistArgs& a, int col4, co
 
 // gs[0..nitems) holds this CTA's local gradient slice; item i is flat float4 column col_of(i).
 // Exchange (multi-GPU), scale, SGD-momentum, store. All threads call it.
+// box != null: the new weights also leave as {value, tag} pairs at box[4 * (col - box_col0) ...]
+// (the mailbox the workers read the conv2 group from).
 template <typename ColFn>
 __device__ __forceinline__ bool exchange_update(const PersistArgs& a, const float4* gs, int nitems,
-                                                ColFn col_of, unsigned seq, bool write_grad) {
+                                                ColFn col_of, unsigned seq, bool write_grad,
+                                                uint2* box = nullptr, int box_col0 = 0,
+                                                unsigned tag = 0u) {
   const int t = threadIdx.x;
   const bool multi = a.multi && a.comm.world > 1;
   if (multi)
@@ -827,10 +567,8 @@ __device__ __forceinline__ bool exchange_update(const PersistArgs& a, const floa
   for (int i = t; i < nitems; i += NT) {
     const int col = col_of(i);
     float4 pv = make_float4(0.f, 0.f, 0.f, 0.f), bv = pv;
-    if (a.update) {   // operands of the update do not depend on the peers: fetch them first
-      pv = ldcg4(a.params + 4 * col);
-      bv = ldcg4(a.mom + 4 * col);
-    }
+    if (a.update || box) pv = ldcg4(a.params + 4 * col);   // operands of the update do not
+    if (a.update) bv = ldcg4(a.mom + 4 * col);             // depend on the peers: fetch them first
     float4 g = gs[i];
     if (multi) {
       ok = ll_gather_sum(a, col, g, seq, g) && ok;
@@ -843,13 +581,19 @@ __device__ __forceinline__ bool exchange_update(const PersistArgs& a, const floa
       reinterpret_cast<float4*>(a.params)[col] = pv;
       reinterpret_cast<float4*>(a.mom)[col] = bv;
     }
+    if (box) {
+      uint4* b4 = reinterpret_cast<uint4*>(box + 4 * (size_t)(col - box_col0));
+      st_volatile_u4(b4, make_uint4(__float_as_uint(pv.x), tag, __float_as_uint(pv.y), tag));
+      st_volatile_u4(b4 + 1, make_uint4(__float_as_uint(pv.z), tag, __float_as_uint(pv.w), tag));
+    }
   }
   return ok;
 }
 
 // Fixed-order sum over `rows` partial rows of the float4 columns [c0, c0 + nc) into gs[0..nc).
 // Thread (rg, c): lanes run along the columns (coalesced), row groups split the rows; a thread's
-// loads are issued 16 at a time so a whole batch costs one L2 round trip.
+// loads are issued U at a time so a whole batch costs one L2 round trip.
+template <int U>
 __device__ __forceinline__ void reduce_rows_slice(const PersistArgs& a, int ls,
                                                   const float* __restrict__ part, int rows,
                                                   int row_floats, int c0, int nc, float4* gs,
@@ -862,22 +606,20 @@ __device__ __forceinline__ void reduce_rows_slice(const PersistArgs& a, int ls,
     float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
     if (rg < RG) {
       const float* p = part + 4 * (size_t)(c0 + cb + c);
-      for (int r0 = rg; r0 < rows; r0 += 16 * RG) {
+      for (int r0 = rg; r0 < rows; r0 += U * RG) {
         // unconditional loads (row index clamped) so all 16 are issued before the first use;
         // a predicated load makes the compiler keep each load next to its add, one L2 round
         // trip per row
-        float4 v[16];
+        float4 v[U];
 #pragma unroll
-        for (int u = 0; u < 16; ++u) v[u] = ldcg4(p + (size_t)min(r0 + u * RG, rows - 1) * row_floats);
+        for (int u = 0; u < U; ++u) v[u] = ldcg4(p + (size_t)min(r0 + u * RG, rows - 1) * row_floats);
 #pragma unroll
-        for (int u = 0; u < 16; ++u)
+        for (int u = 0; u < U; ++u)
           if (r0 + u * RG < rows) { s.x += v[u].x; s.y += v[u].y; s.z += v[u].z; s.w += v[u].w; }
       }
       red[t] = s;
     }
-    PSTAMP(ls, 6);
     __syncthreads();
-    PSTAMP(ls, 7);
     if (t < ncp) {
       float4 acc = red[t];
       for (int g = 1; g < RG; ++g) {
@@ -907,6 +649,359 @@ __device__ __forceinline__ void stage_f4(int count, AddrFn addr, DstFn dst) {
   }
 }
 
+// =========================================================================================
+// WORKER
+// =========================================================================================
+template <bool SPLIT>
+__device__ __forceinline__ void worker_loop(const PersistArgs& a, float* smem) {
+  const WorkerSmem w = carve_worker(smem);
+  const int t = threadIdx.x;
+  const int role = SPLIT ? (int)(blockIdx.x & 1) : 2;
+  const int slot = SPLIT ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int nslots = SPLIT ? a.n_workers >> 1 : a.n_workers;
+  // the halves of the backward this CTA owns
+  const int co0 = SPLIT ? role * 10 : 0, nco = SPLIT ? 10 : C2;
+  const int ci0 = SPLIT ? role * 5 : 0, nci = SPLIT ? 5 : C1;
+  unsigned* ctl = a.ctl;
+
+  if (t == 0) {
+    for (int i = 1; i < 5; ++i) mbar_init(w.bar + i, 1);   // [1] conv2, [2] fc, [3..4] images
+    fence_barrier_init();
+  }
+  const unsigned long long step0 = a.step_ctr[0];
+  const unsigned seq0 = a.multi ? *a.seq_ctr : 0u;
+  const long long idx_base0 = (a.idx_stride != 0 && !a.epoch_begin)
+                                  ? (long long)(step0 - a.step_ctr[1]) * a.idx_stride : 0ll;
+  __syncthreads();
+  if (t == 0) red_release_gpu_add_u32(ctl + C_STARTED * CTL_STRIDE, 1u);
+
+  const int ipc = a.ipc;
+  const int nitems = a.nsteps * ipc;       // (step, image) work items of this CTA, in order
+  const size_t row_bytes = (a.x_mode == 0 || a.x_mode == 3) ? IMG_SZ * 4 : IMG_SZ;
+  const bool is_u8 = (a.x_mode == 1 || a.x_mode == 2);
+  const float inv_B = 1.0f / (float)a.B;
+  float* row2 = a.part2 + (size_t)slot * P2_ROW;
+  uint2* row1 = a.part1 + (size_t)slot * C1_PAIRS;
+
+  // Issue the bulk copy of item k's image (lane 0 of warp 0 only). Returns false if the
+  // item has no image (img >= B) or its data is not there yet and `block` is false.
+  int issued = 0;   // items whose image copy has been issued (thread 0's view)
+  auto item_img = [&](int k, int& ls, int& img) {
+    ls = k / ipc;
+    img = slot + (k - ls * ipc) * nslots;
+  };
+  auto issue_image = [&](int k, bool block) -> bool {
+    int ls, img;
+    item_img(k, ls, img);
+    unsigned long long* bar = w.bar + 3 + (k & 1);
+    if (img >= a.B) {            // ragged tail: nothing to fetch, complete the phase empty
+      mbar_arrive(bar);
+      return true;
+    }
+    if (a.feed_ready) {
+      const unsigned g = a.feed_base + (unsigned)ls;
+      const unsigned want = g + 1u;
+      const unsigned* word = a.feed_ready + 32u * (g & 1u);
+      if (block) {
+        if (!wait_ge(word, want, a, 20u, true)) { mbar_arrive(bar); return true; }
+      } else if ((int)(ld_acquire_sys_u32(word) - want) < 0) {
+        return false;
+      }
+    }
+    size_t r;
+    if (a.x_mode >= 2) r = (size_t)__ldg(a.gidx + idx_base0 + (long long)ls * a.idx_stride + img);
+    else r = (size_t)((a.ring_pos + (unsigned)ls) % (unsigned)a.ring_slots) * a.B + img;
+    const char* src = (const char*)a.x + r * row_bytes;
+    void* dst = is_u8 ? (void*)(w.xu + (k & 1) * 784) : (void*)(w.xs + (k & 1) * IMG_SZ);
+    fence_proxy_async();
+    mbar_expect_tx(bar, (unsigned)row_bytes);
+    bulk_g2s(dst, src, (unsigned)row_bytes, bar);
+    return true;
+  };
+
+  constexpr int FETCH_T = 288;   // lane 0 of warp 9
+  constexpr unsigned long long W2_COPY_DELAY_NS = 900ull;
+  unsigned long long bubble_end_ns = 0ull;
+  constexpr int SIGNAL_T = 300;  // a thread of warp 9 that the backward's wide phases leave idle
+  for (int k = 0; k < nitems; ++k) {
+    int ls, img;
+    item_img(k, ls, img);
+    const bool first_of_step = (k == ls * ipc);
+    const bool last_of_step = (k == ls * ipc + ipc - 1);
+    const bool have = img < a.B;
+    const unsigned long long step = step0 + (unsigned long long)ls;
+
+    // ---- fetch duties belong to ONE thread of warp 9, the warp conv1 leaves idle: it waits
+    // for a parameter group's update, then issues the bulk copy that completes on the
+    // group's mbarrier. conv1's group comes first (it is the last one published).
+    // (the conv2 and fc groups; conv1's 1 KB comes through the tagged mailbox below)
+    auto fetch_fc = [&](bool block) -> bool {
+      const unsigned* ctr = ctl + C_DFC * CTL_STRIDE;
+      const unsigned want = (unsigned)ls * (unsigned)(a.n3 + 1);
+      if (!block && (int)(ld_acquire_gpu_u32(ctr) - want) < 0) return false;
+      if (wait_ge(ctr, want, a, 23u)) {
+        fence_proxy_async();
+        mbar_expect_tx(w.bar + 2, (unsigned)(FLAT_SZ - OFF_W3) * 4u);
+        bulk_g2s(w.P + OFF_W3, a.params + OFF_W3, (unsigned)(FLAT_SZ - OFF_W3) * 4u, w.bar + 2);
+      } else {
+        mbar_arrive(w.bar + 2);   // aborted: complete the phase so nobody hangs on it
+      }
+      return true;
+    };
+    // conv2's weights: at the first step of a launch straight from global memory; afterwards
+    // the {value, tag} mailbox that every worker filled a slice of at the end of the last step
+    // is bulk-copied into the (idle) T buffer and validated word by word after conv1.
+    auto fetch_conv2 = [&]() {
+      fence_proxy_async();
+      if (ls == 0) {
+        mbar_expect_tx(w.bar + 1, (unsigned)P2_ROW * 4u);
+        bulk_g2s(w.P + OFF_W2, a.params + OFF_W2, (unsigned)P2_ROW * 4u, w.bar + 1);
+      } else {
+        mbar_expect_tx(w.bar + 1, (unsigned)P2_ROW * 8u);
+        bulk_g2s(w.Ts, a.w2box, (unsigned)P2_ROW * 8u, w.bar + 1);
+      }
+    };
+    if (t == FETCH_T && issued <= k) { issue_image(k, true); issued = k + 1; }
+    if (t == FETCH_T && first_of_step && ls > 0) {
+      // Every worker published its conv2 slice at the end of its bubble, all within a fraction
+      // of a microsecond of each other. Give the last ones time to land, then pull the whole
+      // mailbox in with one bulk copy that completes under conv1's forward; a word copied too
+      // early is caught by its tag and fetched again.
+      while (globaltimer_ns() - bubble_end_ns < W2_COPY_DELAY_NS) { }
+      fetch_conv2();
+    }
+
+    // dropout masks (Philox keyed by step and sample: replays and the two-kernel path agree)
+    PSTAMP(ls, 0);
+    int tgt = 0;
+    if (have) {
+      if (t >= 32 && t < 32 + C2) {
+        const int c = t - 32;
+        float m = 1.0f;
+        if (a.mask_mode == 1) m = dropout_mask_value(a.seed, step, a.sample_base + img, 0x20000u + c, 0.5f);
+        else if (a.mask_mode == 2) m = a.m2buf[(size_t)img * C2 + c];
+        w.m2s[c] = m;
+      } else if (t >= 64 && t < 64 + FC1) {
+        const int j = t - 64;
+        float m = 1.0f;
+        if (a.mask_mode == 1) m = dropout_mask_value(a.seed, step, a.sample_base + img, 0x30000u + j, 0.5f);
+        else if (a.mask_mode == 2) m = a.m3buf[(size_t)img * FC1 + j];
+        w.m3s[j] = m;
+      }
+    }
+    // ---- image
+    mbar_wait(w.bar + 3 + (k & 1), (unsigned)(k >> 1) & 1u);
+    if (have && t < 32) {
+      // the label is read only now: in host-fed mode the batch is known to have landed once
+      // the image copy completed (the fetch thread waited for the step's ready value)
+      size_t r;
+      if (a.x_mode >= 2) r = (size_t)__ldg(a.gidx + idx_base0 + (long long)ls * a.idx_stride + img);
+      else r = (size_t)((a.label_pos + (unsigned)ls) % (unsigned)a.label_slots) * a.B + img;
+      tgt = (int)__ldcg(a.labels + r);   // ring slots are rewritten while the kernel runs: not via L1
+    }
+    float* xs = w.xs + (k & 1) * IMG_SZ;
+    if (is_u8 && have) {
+      const uchar4* src = reinterpret_cast<const uchar4*>(w.xu + (k & 1) * 784);
+      if (t < IMG_SZ / 4) {
+        const uchar4 v = src[t];
+        reinterpret_cast<float4*>(xs)[t] =
+            make_float4(normalize_px(v.x), normalize_px(v.y), normalize_px(v.z), normalize_px(v.w));
+      }
+    }
+    // ---- conv1's weights: at the first step of a launch from global memory, afterwards from
+    // the mailbox the two conv1 service CTAs fill with {value, tag} pairs. Each of 130 threads
+    // polls its own 16-byte word: the data is the signal, one L2 round trip after it lands.
+    if (first_of_step && t < C1_HALF) {
+      const int e0 = 2 * t;                       // pairs e0, e0 + 1 (same half: 130 is even)
+      const int h = e0 / C1_HALF, i0 = e0 - h * C1_HALF;
+      float v0, v1;
+      if (ls == 0) {
+        v0 = __ldcg(a.params + c1_flat(h, i0));
+        v1 = __ldcg(a.params + c1_flat(h, i0 + 1));
+      } else {
+        const unsigned want = a.tag_base | (unsigned)ls;     // tag of local step ls - 1
+        const uint4* src = reinterpret_cast<const uint4*>(a.w1box) + t;
+        uint4 v = ld_volatile_u4(src);
+        if (!(v.y == want && v.w == want)) {
+          const unsigned long long t0 = globaltimer_ns();
+          for (unsigned polls = 1;; ++polls) {
+            v = ld_volatile_u4(src);
+            if (v.y == want && v.w == want) break;
+            if ((polls & 255u) == 0u) {
+              if (ld_volatile_u32(ctl + C_ABORT * CTL_STRIDE) != 0u) break;
+              if (globaltimer_ns() - t0 > 2ull * a.timeout_ns) { set_abort(a, 20u, 0xffffu, want); break; }
+            }
+          }
+        }
+        v0 = __uint_as_float(v.x);
+        v1 = __uint_as_float(v.z);
+      }
+      w.P[c1_flat(h, i0)] = v0;
+      w.P[c1_flat(h, i0 + 1)] = v1;
+    }
+    if (t == 0) w.flags[0] = (int)ld_volatile_u32(ctl + C_ABORT * CTL_STRIDE);
+    __syncthreads();
+    if (w.flags[0] != 0) break;     // uniform: one thread sampled the abort word
+    PSTAMP(ls, 1);
+    bool fc_issued = !first_of_step;
+    if (t == FETCH_T && first_of_step) {
+      if (ls == 0) fetch_conv2();                // later steps: issued during the wait for conv1's weights
+      fc_issued = fetch_fc(false);               // fc only if it is already published
+    }
+    if (have) conv1_fwd_img(xs, w.P + OFF_W1, w.P + OFF_B1, w.a1s, w.pos1s);
+    if (t == FETCH_T) {
+      if (!fc_issued) fc_issued = fetch_fc(false);
+      // the other image buffer is free (its item has finished): fetch one item ahead
+      if (k + 1 < nitems && issued == k + 1 && issue_image(k + 1, false)) issued = k + 2;
+    }
+    if (first_of_step) {
+      mbar_wait(w.bar + 1, (unsigned)ls & 1u);
+      if (ls > 0) {
+        // unpack the mailbox copy: a word whose tags are not this step's was copied before its
+        // owner had written it; fetch that word again from global memory until it is valid
+        const unsigned want = a.tag_base | (unsigned)ls;
+        const uint4* st4 = reinterpret_cast<const uint4*>(w.Ts);
+        const uint4* box4 = reinterpret_cast<const uint4*>(a.w2box);
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const int i = t + u * NT;
+          if (i < P2_ROW / 2) {
+            uint4 v = st4[i];
+            if (!(v.y == want && v.w == want)) {
+              const unsigned long long t0 = globaltimer_ns();
+              for (unsigned polls = 1;; ++polls) {
+                v = ld_volatile_u4(box4 + i);
+                if (v.y == want && v.w == want) break;
+                if ((polls & 255u) == 0u) {
+                  if (ld_volatile_u32(ctl + C_ABORT * CTL_STRIDE) != 0u) break;
+                  if (globaltimer_ns() - t0 > 2ull * a.timeout_ns) { set_abort(a, 22u, 0xffffu, want); break; }
+                }
+              }
+            }
+            *reinterpret_cast<float2*>(w.P + OFF_W2 + 2 * i) =
+                make_float2(__uint_as_float(v.x), __uint_as_float(v.z));
+          }
+        }
+      }
+    }
+    __syncthreads();
+    PSTAMP(ls, 2);
+    if (have) conv2_fwd_img(w.a1s, w.P + OFF_W2, w.P + OFF_B2, w.m2s, w.a2s, w.pos2s);
+    if (t == FETCH_T && !fc_issued) fetch_fc(true);
+    if (first_of_step) mbar_wait(w.bar + 2, (unsigned)ls & 1u);
+    __syncthreads();
+    PSTAMP(ls, 3);
+    if (have) {
+      fc1_fwd_s(w.a2s, w.P + OFF_W3, w.P + OFF_B3, w.m3s, w.h1s);
+      __syncthreads();
+      PSTAMP(ls, 4);
+      fc2_fwd_img(w.h1s, w.P + OFF_W4, w.P + OFF_B4, w.logit);
+      __syncthreads();
+      float loss_img = 0.0f;
+      if (t < 32) {
+        // log_softmax + NLL + its gradient (src/model.py:22, src/train.py:74), one class per lane
+        const float z = (t < NCLS) ? w.logit[t] : -INFINITY;
+        const float mx = warp_max(z);
+        const float e = (t < NCLS) ? expf(z - mx) : 0.0f;
+        const float lse = mx + logf(warp_sum(e));
+        const float lp = z - lse;
+        if (t < NCLS) w.dlog[t] = (expf(lp) - (t == tgt ? 1.0f : 0.0f)) * inv_B;
+        loss_img = -__shfl_sync(0xffffffffu, lp, tgt) * inv_B;
+      }
+      __syncthreads();
+      PSTAMP(ls, 5);
+      fc2_bwd_img(w.dlog, w.h1s, w.m3s, w.P + OFF_W4, w.dpre, nullptr, nullptr, true, false);
+      __syncthreads();
+      // ---- publish this image's fc operands: the service CTAs form dW3, db3, dW4, db4
+      if (role != 1) {
+        float* act = a.acts + (size_t)img * ACT_STRIDE;
+        act[ACT_A2 + t] = w.a2s[t];                                  // NT == 320 == A2_SZ
+        if (t < FC1) { act[ACT_DPRE + t] = w.dpre[t]; act[ACT_H1 + t] = w.h1s[t]; }
+        if (t < NCLS) act[ACT_DLOG + t] = w.dlog[t];
+        if (t == 0) act[ACT_LOSS] = loss_img;
+      }
+      fc1_bwd_img<true>(w.dpre, w.a2s, w.m2s, w.P + OFF_W3, w.g2s, nullptr, nullptr, true, false);
+      __syncthreads();
+      PSTAMP(ls, 6);
+      build_conv2_dense(w.g2s, w.pos2s, w.m2s, w.Ds, w.live, w.slot_of);
+      __syncthreads();
+      PSTAMP(ls, 7);
+      // Signals are raised by a thread that has no work in the phase that follows (conv2's
+      // weight gradient uses threads 0..275): the CTA barrier above ordered every thread's
+      // stores before its fence, and the fence's wait for L2 acknowledgements costs nobody.
+      if (role != 1 && t == SIGNAL_T) { __threadfence(); signal_add(ctl + C_ACT * CTL_STRIDE); }
+      // conv2's weight gradient first: its reduction then hides behind dgrad + conv1 wgrad
+      if (SPLIT) {
+        conv2_wgrad_part<false>(w.g2s, w.pos2s, w.m2s, w.a1s, row2, row2 + W2_SZ, co0, nco, true);
+      } else {
+        conv2_wgrad_part<true>(w.g2s, w.pos2s, w.m2s, w.a1s, w.acc + OFF_W2, w.acc + OFF_B2, 0, C2,
+                               first_of_step);
+      }
+      PSTAMP(ls, 8);
+      if (SPLIT) __syncthreads();       // every thread's stores of the conv2 partial row are issued
+      if (SPLIT && t == SIGNAL_T) { __threadfence(); signal_add(ctl + C_P2 * CTL_STRIDE); }   // idle in the product
+      conv2_dgrad_T_part(w.Ds, w.live, w.live[C2], w.P + OFF_W2, w.Ts, ci0, nci);
+      __syncthreads();
+      PSTAMP(ls, 9);
+      conv2_dgrad_gather_part(w.Ts, w.a1s, w.g1s, ci0, nci);
+      __syncthreads();
+      PSTAMP(ls, 10);
+      if (SPLIT) {
+        // an idle thread makes sure every CTA's conv2 partial row is there (they were
+        // signalled two phases ago, so this returns at once) while the others finish conv1
+        if (t == SIGNAL_T)
+          w.flags[1] = wait_ge(ctl + C_P2 * CTL_STRIDE, (unsigned)(ls + 1) * (unsigned)a.n_workers, a, 31u) ? 1 : 0;
+        conv1_wgrad_half(w.g1s, w.pos1s, xs, row1, role, a.tag_base | (unsigned)(ls + 1));
+        __syncthreads();                // xs / g1s are reused by the next item
+        PSTAMP(ls, 11);
+      } else {
+        conv1_wgrad_img(w.g1s, w.pos1s, xs, w.acc + OFF_W1, w.acc + OFF_B1, first_of_step);
+        __syncthreads();
+      }
+    }
+    if (!SPLIT && last_of_step) {
+      // several images per CTA: one partial row per step, written once
+      if (slot < a.B) {
+        for (int i = t; i < P2_ROW / 4; i += NT)
+          reinterpret_cast<float4*>(row2)[i] = reinterpret_cast<const float4*>(w.acc + OFF_W2)[i];
+        if (t < C1_PAIRS) {
+          const int h = t / C1_HALF, i = t - h * C1_HALF;
+          st_pair(row1 + t, w.acc[c1_flat(h, i)], a.tag_base | (unsigned)(ls + 1));
+        }
+        __threadfence();
+        __syncthreads();
+        if (t == 0) {
+          signal_add(ctl + C_P2 * CTL_STRIDE);
+          w.flags[1] = wait_ge(ctl + C_P2 * CTL_STRIDE, (unsigned)(ls + 1) * (unsigned)a.n_workers, a, 31u) ? 1 : 0;
+        }
+        __syncthreads();
+      }
+    }
+    if (last_of_step) {
+      // ---- the bubble between two steps (conv1's gradients are on their way to the service
+      // CTAs and back): every worker sums its slice of the conv2 partial rows, exchanges it with
+      // the peers, applies SGD-momentum and publishes the new weights as {value, tag} pairs.
+      if (w.flags[1] == 0) break;
+      const int total = P2_ROW / 4;                                   // 1255 float4 columns
+      const int per = (total + a.n_workers - 1) / a.n_workers;
+      const int c0 = (int)blockIdx.x * per, nc = max(0, min(per, total - c0));
+      float4* gs = reinterpret_cast<float4*>(w.Ts);
+      float4* red = gs + ((per + 3) & ~3);
+      reduce_rows_slice<4>(a, ls, a.part2, a.rows, P2_ROW, c0, nc, gs, red);
+      const bool ok = exchange_update(a, gs, nc, [=](int i) { return OFF_W2 / 4 + c0 + i; },
+                                      seq0 + (unsigned)ls + 1u, a.grad_out != nullptr && ls == a.nsteps - 1,
+                                      a.w2box, OFF_W2 / 4, a.tag_base | (unsigned)(ls + 1));
+      if (!ok) atomicExch(ctl + C_ABORT * CTL_STRIDE, 1u);
+      __syncthreads();               // the T buffer is the next step's mailbox landing zone
+      if (t == FETCH_T) bubble_end_ns = globaltimer_ns();
+      PSTAMP(ls, 12);
+    }
+  }
+}
+
+// =========================================================================================
+// SERVICE
+// =========================================================================================
 // ---- conv1 service: one CTA per half (130 gradients) ---------------------------------------
 // Polls the workers' {value, tag} rows, sums them in row order, exchanges with the peers,
 // applies SGD-momentum out of registers and answers with {new weight, tag} pairs. Nothing on
@@ -1049,6 +1144,7 @@ __device__ __forceinline__ void service_conv1(const PersistArgs& a, float* smem,
       const bool aborted = ld_volatile_u32(ctl + C_ABORT * CTL_STRIDE) != 0u;
       if (!aborted) {
         a.step_ctr[0] = step0 + (unsigned long long)a.nsteps;
+        if (a.epoch_begin) a.step_ctr[1] = step0;
         if (a.multi) *a.seq_ctr = seq0 + (unsigned)a.nsteps;
       }
     }
@@ -1064,9 +1160,10 @@ __device__ __forceinline__ void service_loop(const PersistArgs& a, float* smem) 
   const int t = threadIdx.x;
   const int sidx = (int)blockIdx.x - a.n_workers;
   unsigned* ctl = a.ctl;
-  // kind: 0 conv1 half (two CTAs), 1 small fc (+ loss), 2 conv2 slice, 3 W3 column slice
-  const int kind = sidx < 2 ? 0 : sidx == 2 ? 1 : (sidx < 3 + a.n2 ? 2 : 3);
-  const int part = kind == 0 ? sidx : kind == 2 ? sidx - 3 : kind == 3 ? sidx - 3 - a.n2 : 0;
+  // kind: 0 conv1 half (two CTAs), 1 small fc (+ loss), 3 W3 column slice
+  // (conv2's partial rows are summed by the workers themselves between two steps)
+  const int kind = sidx < 2 ? 0 : sidx == 2 ? 1 : 3;
+  const int part = kind == 0 ? sidx : kind == 3 ? sidx - 3 : 0;
   const unsigned long long step0 = a.step_ctr[0];
   const unsigned seq0 = a.multi ? *a.seq_ctr : 0u;
   __syncthreads();
@@ -1075,7 +1172,6 @@ __device__ __forceinline__ void service_loop(const PersistArgs& a, float* smem) 
     service_conv1(a, smem, part, step0, seq0);
     return;
   }
-  const int arrivals_p = a.split ? 2 * a.B : a.rows;   // producers of a partial-row set per step
   const int B = a.B;
 
   for (int ls = 0; ls < a.nsteps; ++ls) {
@@ -1083,19 +1179,7 @@ __device__ __forceinline__ void service_loop(const PersistArgs& a, float* smem) 
     const bool wg = a.grad_out != nullptr && ls == a.nsteps - 1;
     bool ok = true;
     PSTAMP(ls, 0);
-    if (kind == 2) {
-      // ---------------- conv2 partial rows
-      if (t == 0) sv.flags[0] = wait_ge(ctl + C_P2 * CTL_STRIDE, (unsigned)(ls + 1) * (unsigned)arrivals_p, a, 32u) ? 1 : 0;
-      __syncthreads();
-      if (!sv.flags[0]) break;
-      PSTAMP(ls, 1);
-      const int total = P2_ROW / 4;                 // 1255
-      const int per = (total + a.n2 - 1) / a.n2;
-      const int c0 = part * per, nc = max(0, min(per, total - c0));
-      reduce_rows_slice(a, ls, a.part2, a.rows, P2_ROW, c0, nc, sv.gs, sv.red);
-      PSTAMP(ls, 2);
-      ok = exchange_update(a, sv.gs, nc, [=](int i) { return OFF_W2 / 4 + c0 + i; }, seq, wg);
-    } else {
+    {
       // ---------------- fc gradients from the published activations
       if (t == 0) sv.flags[0] = wait_ge(ctl + C_ACT * CTL_STRIDE, (unsigned)(ls + 1) * (unsigned)B, a, 33u) ? 1 : 0;
       __syncthreads();
@@ -1227,7 +1311,7 @@ __device__ __forceinline__ void service_loop(const PersistArgs& a, float* smem) 
     __threadfence();
     fence_proxy_async();
     __syncthreads();
-    if (t == 0) red_release_gpu_add_u32(ctl + (kind == 2 ? C_D2 : C_DFC) * CTL_STRIDE, 1u);
+    if (t == 0) red_release_gpu_add_u32(ctl + C_DFC * CTL_STRIDE, 1u);
     PSTAMP(ls, 4);
     if (!ok) break;
   }
@@ -1248,24 +1332,22 @@ net_persist_kernel(const __grid_constant__ PersistArgs a) {
 constexpr int PERSIST_SMEM = (WS_BYTES > SV_BYTES ? WS_BYTES : SV_BYTES) + 128;
 
 struct Plan {
-  int grid, n_workers, split, rows, ipc, n_service, n2, n3, kw;
+  int grid, n_workers, split, rows, ipc, n_service, n3, kw;
 };
 
 Plan make_plan(int B) {
   Plan p;
-  const int S = 20;                       // service CTAs: 2 conv1 halves + 1 small fc + n2 conv2 + n3 W3
-  const int maxw = 148 - S;               // 128
+  const int S = 19;                       // service CTAs: 2 conv1 halves + 1 small fc + 16 W3 slices
+  const int maxw = (148 - S) & ~1;        // 128 workers, the rest of the SMs serve
   if (2 * B <= maxw) {
     p.split = 1; p.n_workers = 2 * B; p.rows = B; p.ipc = 1;
   } else {
     p.split = 0; p.n_workers = B < maxw ? B : maxw; p.rows = p.n_workers;
     p.ipc = (B + p.n_workers - 1) / p.n_workers;
   }
-  p.n_service = S;
-  p.n3 = 6;
-  p.n2 = S - 3 - p.n3;
-  const int kw = (A2_SZ + p.n3 - 1) / p.n3;
-  p.kw = (kw + 3) / 4 * 4;                // 56: float4 groups, 50 x 14 = 700 items <= 3 x NT
+  p.n3 = 16;                              // W3 CTAs: 20 columns each, 50 x 5 float4 items = one per thread
+  p.kw = 20;
+  p.n_service = 3 + p.n3;                 // 2 conv1 halves + small fc + W3 slices
   p.grid = p.n_workers + p.n_service;
   return p;
 }
@@ -1297,6 +1379,8 @@ struct B200PersistHost {   // mirrored field by field in ops/persist.py (ctypes.
   unsigned* err;             // 4 u32 (device), used when not multi
   unsigned long long timeout_ns;
   long long* dbg;            // optional phase stamps (b200_net_persist_dbg_words() int64), or null
+  int label_slots; unsigned label_pos;   // direct modes; 0 slots = same ring as the images
+  int epoch_begin; int pad1;
 };
 
 int b200_net_persist_host_size(void) { return (int)sizeof(B200PersistHost); }
@@ -1305,7 +1389,7 @@ int b200_net_persist_host_size(void) { return (int)sizeof(B200PersistHost); }
 int b200_net_persist_plan(int B, int* out9) {
   B200_REQUIRE(B > 0, "b200_net_persist_plan: empty batch");
   const Plan p = make_plan(B);
-  const int o[9] = {p.grid, p.n_workers, p.split, p.rows, p.ipc, p.n_service, p.n2, p.n3, p.kw};
+  const int o[9] = {p.grid, p.n_workers, p.split, p.rows, p.ipc, p.n_service, 0, p.n3, p.kw};
   for (int i = 0; i < 9; ++i) out9[i] = o[i];
   return 0;
 }
@@ -1314,7 +1398,7 @@ int b200_net_persist_plan(int B, int* out9) {
 long long b200_net_persist_scratch_floats(int B) {
   const Plan p = make_plan(B > 0 ? B : 1);
   return (long long)B * ACT_STRIDE + (long long)p.rows * P2_ROW + (long long)p.rows * C1_PAIRS * 2 +
-         C1_PAIRS * 2 + C_NWORDS * CTL_STRIDE + 64;
+         C1_PAIRS * 2 + P2_ROW * 2 + C_NWORDS * CTL_STRIDE + 64;
 }
 
 int b200_net_persist_smem_bytes(void) { return PERSIST_SMEM; }
@@ -1351,15 +1435,19 @@ int b200_net_persist_run(const B200PersistHost* h, void* stream) {
   a.x = h->x; a.labels = h->labels; a.gidx = h->gidx;
   a.x_mode = h->x_mode; a.B = h->B; a.nsteps = h->nsteps; a.update = h->update;
   a.n_workers = p.n_workers; a.split = p.split; a.rows = p.rows; a.ipc = p.ipc;
-  a.n_service = p.n_service; a.n2 = p.n2; a.n3 = p.n3; a.kw = p.kw;
+  a.n_service = p.n_service; a.n3 = p.n3; a.kw = p.kw;
   a.idx_stride = h->idx_stride; a.n_idx = h->n_idx;
   a.ring_slots = h->ring_slots > 0 ? h->ring_slots : 1; a.ring_pos = h->ring_pos;
   a.feed_ready = h->feed_ready; a.feed_consumed = h->feed_consumed; a.feed_base = h->feed_base;
+  a.label_slots = h->label_slots > 0 ? h->label_slots : a.ring_slots;
+  a.label_pos = h->label_slots > 0 ? h->label_pos : a.ring_pos;
+  a.epoch_begin = h->epoch_begin;
   a.acts = h->scratch;
   a.part2 = a.acts + (size_t)h->B * ACT_STRIDE;
   a.part1 = reinterpret_cast<uint2*>(a.part2 + (size_t)p.rows * P2_ROW);
   a.w1box = a.part1 + (size_t)p.rows * C1_PAIRS;
-  a.ctl = reinterpret_cast<unsigned*>(a.w1box + C1_PAIRS);
+  a.w2box = a.w1box + C1_PAIRS;
+  a.ctl = reinterpret_cast<unsigned*>(a.w2box + P2_ROW);
   static std::atomic<unsigned> launch_id{1};
   a.tag_base = (launch_id.fetch_add(1) & 0xffffu) << 16;
   B200_REQUIRE(h->nsteps < 65536, "b200_net_persist_run: at most 65535 steps per launch");
@@ -1417,24 +1505,27 @@ int b200_net_persist_run(const B200PersistHost* h, void* stream) {
     }                                                                                       \
   } while (0)
 
+constexpr int FEED_LABEL_STEPS = 2048;   // label ring (steps): one label copy per launch
+
 struct B200Feeder {
   B200PersistHost tmpl;
   CommDev comm;
-  int R;                    // ring slots (steps)
+  int R;                    // image ring slots (steps)
   size_t x_bytes, y_bytes;  // per step
   char* ringx;
-  long long* ringy;
-  unsigned* flags;          // device: [0] steps copied, [32] steps consumed
+  long long* ringy;         // FEED_LABEL_STEPS steps of labels
+  unsigned* flags;          // device: [0] / [32] steps copied by copy stream 0 / 1, [64] steps consumed
   unsigned fed;             // steps fed since creation
-  cudaStream_t compute, copy;
-  cudaEvent_t join_in, join_compute, join_copy;
+  cudaStream_t compute, copy[2];
+  cudaEvent_t join_in, join_compute, join_copy[2], labels_done;
   long long launches;
 };
 
 int b200_feeder_create(const B200PersistHost* tmpl, int ring_slots, void** out) {
   B200_REQUIRE(tmpl && out, "b200_feeder_create: null argument");
   B200_REQUIRE(tmpl->x_mode == 0 || tmpl->x_mode == 1, "b200_feeder_create: x_mode must be 0 (fp32) or 1 (uint8)");
-  B200_REQUIRE(ring_slots >= 4 && ring_slots % 2 == 0, "b200_feeder_create: ring_slots must be even and >= 4");
+  B200_REQUIRE(ring_slots >= 8 && ring_slots % 4 == 0 && FEED_LABEL_STEPS % ring_slots == 0,
+               "b200_feeder_create: ring_slots must be a multiple of 4, >= 8, dividing %d", FEED_LABEL_STEPS);
   {
     DRVP(cuStreamWriteValue32)
     DRVP(cuStreamWaitValue32)
@@ -1451,18 +1542,88 @@ int b200_feeder_create(const B200PersistHost* tmpl, int ring_slots, void** out) 
   f->x_bytes = (size_t)tmpl->B * 784 * (tmpl->x_mode == 0 ? 4 : 1);
   f->y_bytes = (size_t)tmpl->B * sizeof(long long);
   B200_CUDA_OK(cudaMalloc((void**)&f->ringx, (size_t)f->R * f->x_bytes));
-  B200_CUDA_OK(cudaMalloc((void**)&f->ringy, (size_t)f->R * f->y_bytes));
-  B200_CUDA_OK(cudaMalloc((void**)&f->flags, 64 * sizeof(unsigned)));
+  B200_CUDA_OK(cudaMalloc((void**)&f->ringy, (size_t)FEED_LABEL_STEPS * f->y_bytes));
+  B200_CUDA_OK(cudaMalloc((void**)&f->flags, 96 * sizeof(unsigned)));
   B200_CUDA_OK(cudaMemset(f->ringx, 0, (size_t)f->R * f->x_bytes));
-  B200_CUDA_OK(cudaMemset(f->ringy, 0, (size_t)f->R * f->y_bytes));
-  B200_CUDA_OK(cudaMemset(f->flags, 0, 64 * sizeof(unsigned)));
+  B200_CUDA_OK(cudaMemset(f->ringy, 0, (size_t)FEED_LABEL_STEPS * f->y_bytes));
+  B200_CUDA_OK(cudaMemset(f->flags, 0, 96 * sizeof(unsigned)));
   B200_CUDA_OK(cudaStreamCreateWithFlags(&f->compute, cudaStreamNonBlocking));
-  B200_CUDA_OK(cudaStreamCreateWithFlags(&f->copy, cudaStreamNonBlocking));
   B200_CUDA_OK(cudaEventCreateWithFlags(&f->join_in, cudaEventDisableTiming));
   B200_CUDA_OK(cudaEventCreateWithFlags(&f->join_compute, cudaEventDisableTiming));
-  B200_CUDA_OK(cudaEventCreateWithFlags(&f->join_copy, cudaEventDisableTiming));
+  B200_CUDA_OK(cudaEventCreateWithFlags(&f->labels_done, cudaEventDisableTiming));
+  for (int p = 0; p < 2; ++p) {
+    B200_CUDA_OK(cudaStreamCreateWithFlags(&f->copy[p], cudaStreamNonBlocking));
+    B200_CUDA_OK(cudaEventCreateWithFlags(&f->join_copy[p], cudaEventDisableTiming));
+  }
   B200_CUDA_OK(cudaDeviceSynchronize());
   *out = f;
+  return 0;
+}
+
+// One launch of at most FEED_LABEL_STEPS steps. Stream operations per step: ONE host->device
+// copy (the images) and ONE 32-bit stream write (the step has landed), alternating between two
+// copy streams so two copy engines work at once; the labels of the whole launch go up in one
+// copy beforehand (they are 8 bytes per sample).
+static int feeder_launch(B200Feeder* f, const char* px, const long long* hy, int steps, float* dloss) {
+  DRVP(cuStreamWriteValue32)
+  DRVP(cuStreamWaitValue32)
+  const unsigned R = (unsigned)f->R, half = R / 2u;
+  B200PersistHost a = f->tmpl;
+  a.x = f->ringx;
+  a.labels = f->ringy;
+  a.gidx = nullptr;
+  a.nsteps = steps;
+  a.update = 1;
+  a.grad_out = nullptr;
+  a.idx_stride = 0;
+  a.ring_slots = f->R;
+  a.ring_pos = f->fed % R;
+  a.label_slots = FEED_LABEL_STEPS;
+  a.label_pos = f->fed % (unsigned)FEED_LABEL_STEPS;
+  a.feed_ready = f->flags;
+  a.feed_consumed = f->flags + 64;
+  a.feed_base = f->fed;
+  a.host_loss = dloss;
+  a.epoch_begin = 0;
+  // labels: one or two contiguous pieces of the label ring
+  {
+    const unsigned pos = a.label_pos;
+    const unsigned first = (unsigned)steps < FEED_LABEL_STEPS - pos ? (unsigned)steps : FEED_LABEL_STEPS - pos;
+    B200_CUDA_OK(cudaMemcpyAsync(f->ringy + (size_t)pos * f->tmpl.B, hy, (size_t)first * f->y_bytes,
+                                 cudaMemcpyHostToDevice, f->copy[0]));
+    if (first < (unsigned)steps)
+      B200_CUDA_OK(cudaMemcpyAsync(f->ringy, hy + (size_t)first * f->tmpl.B,
+                                   (size_t)(steps - first) * f->y_bytes, cudaMemcpyHostToDevice, f->copy[0]));
+    B200_CUDA_OK(cudaEventRecord(f->labels_done, f->copy[0]));
+    B200_CUDA_OK(cudaStreamWaitEvent(f->copy[1], f->labels_done, 0));
+  }
+  // The first batches go up BEFORE the kernel is launched (the launch costs the host ~15 us,
+  // during which the copy engines would otherwise sit idle); the kernel then finds its first
+  // inputs in place, and the rest of the copies run ahead of it.
+  const int pre = steps < 4 ? steps : 4;
+  for (int i = 0; i < steps; ++i) {
+    if (i == pre) {
+      if (int e = b200_net_persist_run(&a, f->compute)) return e;
+      ++f->launches;
+    }
+    const unsigned g = f->fed + (unsigned)i;
+    const unsigned p = g & 1u;
+    // first step of a half-ring window on this stream: the slots it is about to refill must
+    // have been consumed (steps below g - p - R/2)
+    if (g >= R && (g - p) % half == 0u)
+      CUP_OK(fn_cuStreamWaitValue32((CUstream)f->copy[p], (CUdeviceptr)(f->flags + 64), (g - p) - half,
+                                    CU_STREAM_WAIT_VALUE_GEQ));
+    const unsigned slot = g % R;
+    B200_CUDA_OK(cudaMemcpyAsync(f->ringx + (size_t)slot * f->x_bytes, px + (size_t)i * f->x_bytes,
+                                 f->x_bytes, cudaMemcpyHostToDevice, f->copy[p]));
+    CUP_OK(fn_cuStreamWriteValue32((CUstream)f->copy[p], (CUdeviceptr)(f->flags + 32u * p), g + 1u,
+                                   CU_STREAM_WRITE_VALUE_DEFAULT));
+  }
+  if (steps <= pre) {
+    if (int e = b200_net_persist_run(&a, f->compute)) return e;
+    ++f->launches;
+  }
+  f->fed += (unsigned)steps;
   return 0;
 }
 
@@ -1472,12 +1633,10 @@ int b200_feeder_run(void* h, const void* hx, const long long* hy, int steps, flo
                     void* caller_stream) {
   B200Feeder* f = static_cast<B200Feeder*>(h);
   B200_REQUIRE(f && steps > 0, "b200_feeder_run: bad arguments");
-  DRVP(cuStreamWriteValue32)
-  DRVP(cuStreamWaitValue32)
   cudaStream_t cs = (cudaStream_t)caller_stream;
   B200_CUDA_OK(cudaEventRecord(f->join_in, cs));
   B200_CUDA_OK(cudaStreamWaitEvent(f->compute, f->join_in, 0));
-  B200_CUDA_OK(cudaStreamWaitEvent(f->copy, f->join_in, 0));
+  for (int p = 0; p < 2; ++p) B200_CUDA_OK(cudaStreamWaitEvent(f->copy[p], f->join_in, 0));
   float* dloss = nullptr;
   if (hloss) {
     // the kernel writes the losses into the caller's pinned buffer through its device alias
@@ -1489,43 +1648,26 @@ int b200_feeder_run(void* h, const void* hx, const long long* hy, int steps, flo
       return (int)e;
     }
   }
-  B200PersistHost a = f->tmpl;
-  a.x = f->ringx;
-  a.labels = f->ringy;
-  a.gidx = nullptr;
-  a.nsteps = steps;
-  a.update = 1;
-  a.grad_out = nullptr;
-  a.idx_stride = 0;
-  a.ring_slots = f->R;
-  a.ring_pos = f->fed % (unsigned)f->R;
-  a.feed_ready = f->flags;
-  a.feed_consumed = f->flags + 32;
-  a.feed_base = f->fed;
-  a.host_loss = dloss;
-  // the kernel goes first: it is resident and polling when the first batch lands
-  if (int e = b200_net_persist_run(&a, f->compute)) return e;
-  ++f->launches;
-  const unsigned half = (unsigned)f->R / 2u;
   const char* px = static_cast<const char*>(hx);
-  for (int i = 0; i < steps; ++i) {
-    const unsigned g = f->fed + (unsigned)i;
-    if (g >= (unsigned)f->R && g % half == 0u)   // slots of the next half ring must be consumed
-      CUP_OK(fn_cuStreamWaitValue32((CUstream)f->copy, (CUdeviceptr)(f->flags + 32), g - half,
-                                    CU_STREAM_WAIT_VALUE_GEQ));
-    const unsigned slot = g % (unsigned)f->R;
-    B200_CUDA_OK(cudaMemcpyAsync(f->ringx + (size_t)slot * f->x_bytes, px + (size_t)i * f->x_bytes,
-                                 f->x_bytes, cudaMemcpyHostToDevice, f->copy));
-    B200_CUDA_OK(cudaMemcpyAsync(f->ringy + (size_t)slot * f->tmpl.B, hy + (size_t)i * f->tmpl.B,
-                                 f->y_bytes, cudaMemcpyHostToDevice, f->copy));
-    CUP_OK(fn_cuStreamWriteValue32((CUstream)f->copy, (CUdeviceptr)f->flags, g + 1u,
-                                   CU_STREAM_WRITE_VALUE_DEFAULT));
+  for (int done = 0; done < steps;) {
+    const int n = steps - done < FEED_LABEL_STEPS ? steps - done : FEED_LABEL_STEPS;
+    if (done > 0) {
+      // the label ring holds one launch: the next launch's labels may only go up once the
+      // previous kernel has finished with its own
+      B200_CUDA_OK(cudaEventRecord(f->join_compute, f->compute));
+      for (int p = 0; p < 2; ++p) B200_CUDA_OK(cudaStreamWaitEvent(f->copy[p], f->join_compute, 0));
+    }
+    if (int e = feeder_launch(f, px + (size_t)done * f->x_bytes, hy + (size_t)done * f->tmpl.B, n,
+                              dloss ? dloss + done : nullptr))
+      return e;
+    done += n;
   }
-  f->fed += (unsigned)steps;
   B200_CUDA_OK(cudaEventRecord(f->join_compute, f->compute));
   B200_CUDA_OK(cudaStreamWaitEvent(cs, f->join_compute, 0));
-  B200_CUDA_OK(cudaEventRecord(f->join_copy, f->copy));
-  B200_CUDA_OK(cudaStreamWaitEvent(cs, f->join_copy, 0));
+  for (int p = 0; p < 2; ++p) {
+    B200_CUDA_OK(cudaEventRecord(f->join_copy[p], f->copy[p]));
+    B200_CUDA_OK(cudaStreamWaitEvent(cs, f->join_copy[p], 0));
+  }
   return 0;
 }
 
@@ -1535,15 +1677,18 @@ int b200_feeder_destroy(void* h) {
   B200Feeder* f = static_cast<B200Feeder*>(h);
   if (!f) return 0;
   cudaStreamSynchronize(f->compute);
-  cudaStreamSynchronize(f->copy);
+  for (int p = 0; p < 2; ++p) cudaStreamSynchronize(f->copy[p]);
   cudaFree(f->ringx);
   cudaFree(f->ringy);
   cudaFree(f->flags);
   cudaEventDestroy(f->join_in);
   cudaEventDestroy(f->join_compute);
-  cudaEventDestroy(f->join_copy);
+  cudaEventDestroy(f->labels_done);
+  for (int p = 0; p < 2; ++p) {
+    cudaEventDestroy(f->join_copy[p]);
+    cudaStreamDestroy(f->copy[p]);
+  }
   cudaStreamDestroy(f->compute);
-  cudaStreamDestroy(f->copy);
   delete f;
   return 0;
 }

@@ -28,7 +28,8 @@ WORKER = ["wait conv1 weights + image", "conv1 fwd", "conv2 fwd (+ wait conv2 we
           "fc1 fwd (+ wait fc weights)", "fc2 fwd + loss",
           "fc2 bwd (dpre) + publish acts + fc1 bwd (data)", "build dense dconv2",
           "conv2 wgrad (half)", "conv2 dgrad T (half)", "conv2 dgrad gather (half)",
-          "conv1 wgrad (half) + signal"]
+          "conv1 wgrad (half) + tagged stores",
+          "bubble: conv2 slice sum + exchange + SGD + publish"]
 SERVICE = ["wait for producers (conv1: poll + sum rows)", "reduce / batch GEMM",
            "exchange + SGD", "publish"]
 
@@ -70,7 +71,7 @@ def main():
     lines += [f"SM clock {ghz:.3f} GHz; step period seen by the workers: **{period:.2f} us**", "",
               "## Workers (median over CTAs and steady-state steps)", "",
               "| phase | role 0 us | role 1 us |", "|---|---|---|"]
-    nph = 12
+    nph = 13
     tot = [0.0, 0.0]
     for ph in range(nph):
         row = []
@@ -80,7 +81,7 @@ def main():
             t0 = clk[ctas][:, lo:hi, ph - 1] if ph > 0 else None
             if ph == 0:
                 # stamp 0 of step s follows stamp 11 of step s-1
-                prev = clk[ctas][:, lo - 1:hi - 1, 11]
+                prev = clk[ctas][:, lo - 1:hi - 1, 12]
                 dur = (clk[ctas][:, lo:hi, 0] - prev)
                 # phase 0 itself is "top of step"; report the gap end-of-step -> top as part of wait
                 val = float(dur.median() / ghz / 1e3)
@@ -100,10 +101,10 @@ def main():
         vals = [float((clk[c, lo:hi, ph + 1] - clk[c, lo:hi, ph]).median() / ghz / 1e3)
                 for ph in range(4)]
         lines.append(f"| {c} | {kind} | " + " | ".join(f"{v:.2f}" for v in vals) + " |")
-    lines += ["", "## Inside the service compute (us after the wait ended; stamps 5, 6, 7)", ""]
+    lines += ["", "## Inside the service compute (us after the wait ended: staging done, compute done)", ""]
     for i, kind in enumerate(kinds):
         c = W + i
-        vals = [float((clk[c, lo:hi, ph] - clk[c, lo:hi, 1]).median() / ghz / 1e3) for ph in (5, 6, 7)]
+        vals = [float((clk[c, lo:hi, ph] - clk[c, lo:hi, 1]).median() / ghz / 1e3) for ph in (5, 6)]
         lines.append(f"* CTA {c} {kind}: " + ", ".join(f"{v:.2f}" for v in vals))
     # when, inside the step, does each group's publish land relative to the workers' step start
     lines += ["", "## Publish times relative to the median worker step start (us, global timer)", ""]
@@ -111,12 +112,19 @@ def main():
     for name, ctas in (("conv1", [W, W + 1]), ("small fc", [W + 2]),
                        ("conv2 (last CTA)", list(range(W + 3, W + 3 + plan["conv2_ctas"]))),
                        ("W3 (last CTA)", list(range(W + 3 + plan["conv2_ctas"], plan["grid"])))):
+        if not ctas:
+            continue
         pub = gt[ctas][:, lo:hi, 4].max(dim=0).values
         lines.append(f"* {name}: step s published {float((pub - w0).median()) / 1e3:.2f} us after "
                      "the workers started step s")
     wend = gt[:W, lo:hi, 11].max(dim=0).values
     lines.append(f"* last worker finishes step s {float((wend - w0).median()) / 1e3:.2f} us after "
                  "the median worker started it")
+    # start-up: when did each of the first steps begin, relative to the first stamp of the launch
+    t_first = gt[:W, 0, 0].min()
+    starts = [float((gt[:W, i, 0].median() - t_first) / 1e3) for i in range(min(10, S))]
+    lines += ["", "## Start of the first steps after the first CTA's first stamp (us): "
+              + ", ".join(f"{v:.1f}" for v in starts)]
     text = "\n".join(lines) + "\n"
     print(text)
     if a.out:

@@ -263,7 +263,11 @@ def late_rank(rank, world, backend, out_dir, what):
         eng = DP(Net().to(dev), comm).fused_engine(lr=0.02, momentum=0.5)
         bx = torch.randn(4 * 16, 784, device=dev)
         by = torch.randint(0, 10, (4 * 16,), device=dev)
-    comm.all_reduce(x.clone(), op="sum", algo="oneshot")       # everyone healthy: no error
+    # everyone healthy: no error (also creates the algorithm's staging, which is a collective
+    # host-side step and must not be what the late rank holds up)
+    comm.all_reduce(x.clone() if what != "twoshot" else x, op="sum",
+                    algo="oneshot" if what == "persist" else what)
+    x.fill_(float(rank + 1))
     torch.cuda.synchronize()
     comm.check_errors()
     comm.host_barrier()

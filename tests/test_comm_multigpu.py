@@ -129,11 +129,12 @@ def test_mlp_ddp_peer(native_lib, tmp_path, algo):
                                    bf(got_master[s.offset:s.offset + s.numel].view(s.shape)),
                                    rtol=0, atol=0)
     print("mlp update errors vs the rounding oracle:", {k: round(v, 4) for k, v in errs.items()})
-    # what is left is summation order inside the GEMMs and the all-reduce (fp32 accumulation)
-    # and the occasional bf16 rounding flip it causes: a sign error or a dropped rank in any
-    # one tensor would show as an error of order 1
+    # What is left is summation order inside the GEMMs and the all-reduce and the bf16 rounding
+    # flips it causes downstream (measured on 2 GPUs: 0.3 % for the last layer, 2.4-3.1 % for the
+    # two below it, the in-switch NVLS reduction being the largest). A sign error shows as an
+    # error above 1, a dropped rank as 1/world >= 12 %.
     for name, err in errs.items():
-        assert err < 0.03, f"update mismatch {err:.4f} for {name}: {errs}"
+        assert err < 0.05, f"update mismatch {err:.4f} for {name}: {errs}"
 
 
 @pytest.mark.parametrize("kind,bn", [("cta", 128), ("persistent", 256), ("persistent", 128)])
