@@ -494,58 +494,57 @@ __device__ __forceinline__ bool ll_gather_sum(const PersistArgs& a, int col4, co
                                               unsigned seq, float4& out) {
   constexpr int N4 = FLAT_SZ / 4;
   const unsigned slot = seq & 1u;
-  const int W = a.comm.world;
-  const uint4* base = peer_ptr<uint4>(a.comm, a.comm.rank, a.stage_off) +
-                      ((size_t)slot * W * N4 + col4) * 2;
-  float4 val[B200_MAX_WORLD];
-  unsigned pending = ((1u << W) - 1u) & ~(1u << a.comm.rank);
+  const int W = a.comm.world, me = a.comm.rank;
+  const uint4* base = peer_ptr<uint4>(a.comm, me, a.stage_off) + ((size_t)slot * W * N4 + col4) * 2;
   unsigned long long t0 = 0;
   unsigned polls = 0;
-  bool ok = true;
-  while (pending) {
-    // four sources in flight at a time: their eight 16-byte loads are issued back to back
+  for (;;) {
+    // Every source's two words in one go, UNCONDITIONALLY (ranks beyond the world and this rank
+    // itself re-read a valid slot and are ignored): 16 independent loads per round, no local
+    // arrays indexed under a predicate, nothing for the compiler to serialise.
+    uint4 wa[B200_MAX_WORLD], wb[B200_MAX_WORLD];
 #pragma unroll
-    for (int h = 0; h < B200_MAX_WORLD; h += 4) {
-      if (!((pending >> h) & 0xfu)) continue;
-      uint4 wa[4], wb[4];
-#pragma unroll
-      for (int q = 0; q < 4; ++q)
-        if (pending & (1u << (h + q))) {
-          wa[q] = ld_volatile_u4(base + (size_t)(h + q) * N4 * 2);
-          wb[q] = ld_volatile_u4(base + (size_t)(h + q) * N4 * 2 + 1);
-        }
-#pragma unroll
-      for (int q = 0; q < 4; ++q)
-        if ((pending & (1u << (h + q))) && wa[q].y == seq && wa[q].w == seq && wb[q].y == seq &&
-            wb[q].w == seq) {
-          val[h + q] = make_float4(__uint_as_float(wa[q].x), __uint_as_float(wa[q].z),
-                                   __uint_as_float(wb[q].x), __uint_as_float(wb[q].z));
-          pending &= ~(1u << (h + q));
-        }
+    for (int r = 0; r < B200_MAX_WORLD; ++r) {
+      const int rr = (r < W) ? r : me;
+      wa[r] = ld_volatile_u4(base + (size_t)rr * N4 * 2);
+      wb[r] = ld_volatile_u4(base + (size_t)rr * N4 * 2 + 1);
     }
-    if (pending && (++polls & 255u) == 0u) {
+    unsigned missing = 0;
+#pragma unroll
+    for (int r = 0; r < B200_MAX_WORLD; ++r)
+      if (r < W && r != me &&
+          !(wa[r].y == seq && wa[r].w == seq && wb[r].y == seq && wb[r].w == seq))
+        missing |= 1u << r;
+    if (!missing) {
+      float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int r = 0; r < B200_MAX_WORLD; ++r)      // rank order: bit-identical on every rank
+        if (r < W) {
+          const float4 v = (r == me) ? mine
+                                     : make_float4(__uint_as_float(wa[r].x), __uint_as_float(wa[r].z),
+                                                   __uint_as_float(wb[r].x), __uint_as_float(wb[r].z));
+          s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+        }
+      out = s;
+      return true;
+    }
+    if ((++polls & 127u) == 0u) {
       if (t0 == 0) t0 = globaltimer_ns();
-      if (ld_volatile_u32(a.ctl + C_ABORT * CTL_STRIDE) != 0u) { ok = false; break; }
-      if (globaltimer_ns() - t0 > a.timeout_ns) {
-        const int peer = __ffs((int)pending) - 1;
+      bool give_up = ld_volatile_u32(a.ctl + C_ABORT * CTL_STRIDE) != 0u;
+      if (!give_up && globaltimer_ns() - t0 > a.timeout_ns) {
+        const int peer = __ffs((int)missing) - 1;
         if (atomicCAS(a.comm.err, 0u, 1u) == 0u) {
           a.comm.err[1] = (unsigned)peer; a.comm.err[2] = 12u; a.comm.err[3] = seq;
         }
         atomicExch(a.ctl + C_ABORT * CTL_STRIDE, 1u);
-        ok = false;
-        break;
+        give_up = true;
+      }
+      if (give_up) {
+        out = make_float4(mine.x * W, mine.y * W, mine.z * W, mine.w * W);   // any finite value: the run is aborted
+        return false;
       }
     }
   }
-  float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-  for (int r = 0; r < B200_MAX_WORLD; ++r)
-    if (r < W) {
-      const float4 v = (r == a.comm.rank || !ok) ? mine : val[r];
-      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
-    }
-  out = s;
-  return ok;
 }
 
 // gs[0..nitems) holds this CTA's local gradient slice; item i is flat float4 column col_of(i).

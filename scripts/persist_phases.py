@@ -40,7 +40,15 @@ def main():
     ap.add_argument("--steps", type=int, default=24)
     ap.add_argument("--out", default="")
     a = ap.parse_args()
-    dev = torch.device("cuda", 0)
+    import os
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    comm = None
+    if world > 1:   # run under torchrun: every rank runs the launch, rank 0 reports its own CTAs
+        from csed_514_project_distributed_training_using_pytorch_b200 import parallel as P
+        torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)))
+        comm = P.init_process_group("b200", rank=rank, world_size=world)
+    dev = torch.device("cuda", torch.cuda.current_device())
     B, S = a.batch, a.steps
     plan = persist_plan(B)
     g = torch.Generator().manual_seed(0)
@@ -49,7 +57,11 @@ def main():
     y = torch.randint(0, 10, (n,), generator=g).to(dev)
     perm = torch.randperm(n, generator=g).to(torch.int32).to(dev)
     torch.manual_seed(1)
-    eng = PersistentNetEngine(Net().to(dev).train(), lr=0.02, momentum=0.5)
+    if comm is not None:
+        from csed_514_project_distributed_training_using_pytorch_b200.parallel.data_parallel import DataParallel
+        eng = DataParallel(Net().to(dev).train(), comm).fused_engine(lr=0.02, momentum=0.5)
+    else:
+        eng = PersistentNetEngine(Net().to(dev).train(), lr=0.02, momentum=0.5)
     eng.begin_epoch()
     eng.run_steps(x, y, X_F32_GATHER, gidx=perm, batch=B, nsteps=S, idx_stride=B)   # warm-up
     torch.cuda.synchronize()
@@ -57,11 +69,17 @@ def main():
     eng.run_steps(x, y, X_F32_GATHER, gidx=perm, batch=B, nsteps=S, idx_stride=B)
     torch.cuda.synchronize()
     eng.check_errors()
+    if comm is not None:
+        comm.host_barrier()
+        if rank != 0:
+            P.destroy_process_group()
+            return
     d = dbg.cpu()
     clk, gt = d[..., 0].double(), d[..., 1].double()
     W = plan["workers"]
     lo, hi = 4, min(S, d.shape[1]) - 1          # steady-state steps
-    lines = [f"# Persistent step kernel: phase timeline, batch {B}, {S} steps per launch", "",
+    lines = [f"# Persistent step kernel: phase timeline, batch {B}, {S} steps per launch, "
+             f"{world} GPU(s) (rank 0's CTAs)", "",
              f"Plan: {plan}", ""]
     # SM clock from the two time bases (cycles per ns over the whole launch, CTA 0)
     cyc = clk[0, hi, 0] - clk[0, lo, 0]
@@ -129,6 +147,8 @@ def main():
     print(text)
     if a.out:
         Path(a.out).write_text(text)
+    if comm is not None:
+        P.destroy_process_group()
 
 
 if __name__ == "__main__":
