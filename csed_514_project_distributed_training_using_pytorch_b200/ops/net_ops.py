@@ -84,10 +84,18 @@ class Conv2DropPoolRelu(torch.autograd.Function):
         pos2 = torch.empty(B, 20, 4, 4, dtype=torch.uint8, device=a1.device)
         if mask_mode == 1 and mask is None:
             mask = torch.empty(B, 20, dtype=torch.float32, device=a1.device)
-        # "tcgen05": TF32 implicit GEMM on the tensor cores (csrc/conv_tcgen05.cu);
+        # "tc": TF32 implicit GEMM without im2col, TMA-fed (csrc/conv2_tc.cu);
+        # "tcgen05": the first tensor-core version with an in-smem im2col (csrc/conv_tcgen05.cu);
         # "simt": fp32-exact CUDA-core kernel (csrc/net_kernels.cu)
-        N.call("b200_conv2_fwd_tc" if impl == "tcgen05" else "b200_conv2_fwd", N.ptr(a1), N.ptr(w), N.ptr(b), N.ptr(mask), mask_mode, float(p),
-               int(seed), int(step), N.ptr(a2), N.ptr(pos2), B, N.stream())
+        if impl == "tc":
+            c4 = torch.empty(B, 4, 12, 12, 4, dtype=torch.float32, device=a1.device)
+            N.call("b200_a1_to_c4", N.ptr(a1), N.ptr(c4), B, N.stream())
+            N.call("b200_conv2_fwd_tc2", N.ptr(c4), N.ptr(w), N.ptr(b), N.ptr(mask), mask_mode, float(p),
+                   int(seed), int(step), N.ptr(a2), N.ptr(pos2), B, N.stream())
+        else:
+            N.call("b200_conv2_fwd_tc" if impl == "tcgen05" else "b200_conv2_fwd", N.ptr(a1), N.ptr(w),
+                   N.ptr(b), N.ptr(mask), mask_mode, float(p),
+                   int(seed), int(step), N.ptr(a2), N.ptr(pos2), B, N.stream())
         ctx.save_for_backward(a1, w, a2, pos2, mask if mask_mode else None)
         return a2
 

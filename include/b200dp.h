@@ -202,6 +202,14 @@ int b200_gemm_plan(int M, int N, int K, int rs_on, int both_mn, int* kind, int* 
 int b200_conv2_fwd_tc(const float* a1, const float* w, const float* b, float* mask, int mask_mode,
                       float p, unsigned long long seed, unsigned long long step, float* a2,
                       void* pos2, int B, void* stream);
+/* conv2 as an implicit GEMM WITHOUT im2col (csrc/conv2_tc.cu): activations in the c4 layout
+ * [B][4 chunks][12][12][4 floats] arrive by one 5-D TMA load per image pair, every filter tap is
+ * a descriptor start-address shift, 50 tcgen05.mma.kind::tf32 per pair, pool/ReLU/Dropout2d in the
+ * TMEM epilogue. Same outputs as b200_conv2_fwd. Ref: src/model.py:17 */
+int b200_a1_to_c4(const float* a1, float* c4, int B, void* stream);
+int b200_conv2_fwd_tc2(const float* a1_c4, const float* w, const float* b, float* mask, int mask_mode,
+                       float p, unsigned long long seed, unsigned long long step, float* a2,
+                       void* pos2, int B, void* stream);
 /* MLP helpers: fused softmax + NLL + gradient, bias gradient, master-weight SGD. */
 int b200_softmax_nll_bf16(const float* logits, int ld, int ncls, const long long* labels,
                           float* loss, void* dlogits, int ld_d, int B, void* stream);

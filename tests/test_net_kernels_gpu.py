@@ -263,6 +263,25 @@ def test_native_runner_matches_python_loop(cuda_device):
     assert (out[0][1] > 1.5).all() and (out[0][1] < 3.5).all()
 
 
+@pytest.mark.parametrize("B", [1, 2, 7, 64, 200, 512, 1000])
+def test_conv2_tc_implicit_gemm_matches_oracle(cuda_device, B):
+    """conv2 forward as a TMA-fed implicit GEMM without im2col (csrc/conv2_tc.cu, TF32) vs the
+    fp64 oracle of the layer and vs the SIMT kernel, arg-max positions included."""
+    torch.manual_seed(1)
+    net = Net()
+    g = torch.Generator().manual_seed(B)
+    a1 = torch.relu(torch.randn(B, 10, 12, 12, generator=g))
+    m2 = oracle.make_masks(B, g)[0]
+    conv = torch.nn.functional.conv2d(a1.double(), net.conv2.weight.double(), net.conv2.bias.double())
+    want = torch.relu(torch.nn.functional.max_pool2d(conv * m2.double().view(B, 20, 1, 1), 2)).float()
+    args = (a1.to(cuda_device), net.conv2.weight.to(cuda_device), net.conv2.bias.to(cuda_device),
+            m2.to(cuda_device), 2)
+    got = net_ops.conv2_drop_pool_relu(*args, impl="tc")
+    torch.testing.assert_close(got.cpu(), want, rtol=5e-3, atol=5e-3)   # TF32 inputs
+    simt = net_ops.conv2_drop_pool_relu(*args)
+    torch.testing.assert_close(got, simt, rtol=5e-3, atol=5e-3)
+
+
 @pytest.mark.parametrize("B", [1, 2, 7, 64, 1000])
 def test_conv2_tcgen05_matches_oracle(cuda_device, B):
     """conv2 + dropout2d + pool + relu on tcgen05 (TF32) vs the fp32 oracle of the layer."""
