@@ -83,6 +83,28 @@ def _crossover_table() -> dict:
     return _CROSSOVER
 
 
+def choose_from_table(world: int, nbytes: int, nvls_ok: bool = False) -> int:
+    """Algorithm for a bucket of `nbytes` on `world` ranks from the measured table
+    (profiles/allreduce_crossover.json, written from the sweep): 0 tagged one-shot while the
+    bytes every rank must absorb stay small, 2 NVLS (reduction inside the NVSwitch) in the
+    range where it won and only if the bucket lives in the multicast region (`nvls_ok`),
+    1 two-shot otherwise. World sizes without a measured row use the nearest measured one."""
+    if "B200DP_ONESHOT_MAX_KB" not in os.environ:
+        tab_all = {k: v for k, v in _crossover_table().items() if k.isdigit()}
+        tab = tab_all.get(str(world))
+        if tab is None and tab_all:
+            tab = tab_all[str(min((int(k) for k in tab_all), key=lambda k: abs(k - world)))]
+        if tab is not None:
+            if nbytes <= tab["oneshot_max_bytes"]:
+                return 0
+            if nvls_ok and "nvls_min_bytes" in tab and \
+                    tab["nvls_min_bytes"] <= nbytes <= tab.get("nvls_max_bytes", 1 << 62):
+                return 2
+            return 1
+    budget = int(os.environ.get("B200DP_ONESHOT_MAX_KB", "256")) << 10
+    return 0 if nbytes * max(1, world - 1) <= budget else 1
+
+
 class _RawCudaMemory:
     """Exposes a raw device allocation to torch through __cuda_array_interface__."""
 
@@ -485,16 +507,9 @@ class PeerComm(BaseComm):
         return {"comm": self._blob, "stage_off": ch["stage"], "src_bytes": ch["src_bytes"],
                 "slice_vec": sl, "seq": ch["seq"]}
 
-    def choose_algo(self, nbytes: int) -> int:
-        """Measured crossover (profiles/allreduce_sweep.md): the tagged one-shot wins while the
-        bytes every rank must absorb, (world-1) x payload, stay small (<= 1 MiB at 2 GPUs,
-        <= 32 KiB at 8); the two-shot wins above."""
-        if "B200DP_ONESHOT_MAX_KB" not in os.environ:
-            tab = _crossover_table().get(str(self.world_size))
-            if tab is not None:          # measured on this kind of box for this world size
-                return 0 if nbytes <= tab["oneshot_max_bytes"] else 1
-        budget = int(os.environ.get("B200DP_ONESHOT_MAX_KB", "256")) << 10
-        return 0 if nbytes * max(1, self.world_size - 1) <= budget else 1
+    def choose_algo(self, nbytes: int, nvls_ok: bool = False) -> int:
+        """0 one-shot, 1 two-shot, 2 NVLS for a bucket of `nbytes` (see `choose_from_table`)."""
+        return choose_from_table(self.world_size, nbytes, nvls_ok)
 
     def all_reduce(self, tensor: torch.Tensor, op: str = "mean", algo="auto", blocks: int = 0,
                    sgd=None, channel: int = 0, push_from: int = 0):
@@ -511,8 +526,10 @@ class PeerComm(BaseComm):
             raise CommError("all_reduce size must be a multiple of 16 bytes (pad the bucket)")
         if algo == "nvls" or algo == 2:
             return self._all_reduce_nvls(tensor, op, sgd, channel, blocks)
-        a = {"auto": self.choose_algo(nbytes), "oneshot": 0, "twoshot": 1}[algo] \
-            if isinstance(algo, str) else int(algo)
+        a = {"auto": self.choose_algo(nbytes, self.nvls_offset_of(tensor) is not None),
+             "oneshot": 0, "twoshot": 1}[algo] if isinstance(algo, str) else int(algo)
+        if a == 2:
+            return self._all_reduce_nvls(tensor, op, sgd, channel, blocks)
         W = self.world_size
         nvec = nbytes // 16
         need = 2 * nbytes if a == 0 else ((nvec + W - 1) // W) * 16   # one-shot stages tagged words

@@ -24,12 +24,17 @@ from ..utils.flat import FlatParams
 from .reducer import Reducer
 
 
+def module_bytes(module: nn.Module) -> int:
+    return sum(p.numel() * p.element_size() for p in module.parameters())
+
+
 class DataParallel(nn.Module):
     def __init__(self, module: nn.Module, comm=None, bucket_of: Optional[Sequence[int]] = None,
                  fuse_sgd=None, algo="auto", broadcast_from: int = 0):
-        """algo: "auto" | "oneshot" | "twoshot" | "nvls". "nvls" places the gradient buckets in
-        the multicast (NVLink SHARP) region so the switch reduces them; it falls back to
-        "twoshot" when the machine does not offer multicast."""
+        """algo: "auto" | "oneshot" | "twoshot" | "nvls". "auto" (the default, like the
+        reference's knob-free `DDP(model)`, src/train_dist.py:63) picks one-shot, two-shot or
+        NVLS per bucket from the measured crossover table; "nvls" forces the in-switch reduction
+        and falls back to "twoshot" when the machine does not offer multicast."""
         super().__init__()
         if comm is None:
             from .process_group import get_comm
@@ -38,11 +43,17 @@ class DataParallel(nn.Module):
         self.comm = comm
         self._verify_shapes()
         grad_alloc = None
-        if algo == "nvls":
-            if hasattr(comm, "nvls_init") and comm.world_size > 1 and comm.nvls_init():
+        self.nvls = False
+        if algo in ("nvls", "auto") and hasattr(comm, "nvls_init") and comm.world_size > 1 \
+                and module_bytes(module) >= (1 << 20):
+            # gradient buckets live in the multicast-bound region whenever the machine offers
+            # NVLS, so "auto" can pick the in-switch reduction per bucket from the measured table
+            # (tiny models stay in the plain arena: their buckets are one-shot territory)
+            if comm.nvls_init():
                 grad_alloc = comm.alloc_nvls
-            else:
-                algo = "twoshot"
+                self.nvls = True
+        if algo == "nvls" and not self.nvls:
+            algo = "twoshot"
         self.flat = FlatParams(module, alloc=comm.alloc, grad_alloc=grad_alloc)
         # init_sync: rank 0's parameters (and buffers) win (torch DDP default)
         if comm.world_size > 1:

@@ -168,7 +168,11 @@ class Reducer:
 
     def _algo_for(self, nbytes: int) -> int:
         if self.algo == "auto":
-            return self.comm.choose_algo(nbytes) if hasattr(self.comm, "choose_algo") else 0
+            if not hasattr(self.comm, "choose_algo"):
+                return 0
+            nvls_ok = hasattr(self.comm, "nvls_offset_of") and \
+                self.comm.nvls_offset_of(self.flat.grad) is not None
+            return self.comm.choose_algo(nbytes, nvls_ok)
         return {"oneshot": 0, "twoshot": 1, "nvls": 2}[self.algo]
 
     def set_lr(self, lr: float):

@@ -14,13 +14,15 @@ from csed_514_project_distributed_training_using_pytorch_b200 import parallel as
 from csed_514_project_distributed_training_using_pytorch_b200.models.mlp import WideMLP, LocalSink, MasterSGD
 from csed_514_project_distributed_training_using_pytorch_b200.parallel.data_parallel import DataParallel
 from csed_514_project_distributed_training_using_pytorch_b200.utils.flat import FlatParams
+from csed_514_project_distributed_training_using_pytorch_b200.utils.clocks import ClockSampler
+from _nccl import nccl_group
 
 ap = argparse.ArgumentParser()
 ap.add_argument("--batch", type=int, default=512)
 ap.add_argument("--steps", type=int, default=50)
 ap.add_argument("--warmup", type=int, default=10)
 ap.add_argument("--skip-torch", action="store_true")
-ap.add_argument("--algo", default="twoshot", choices=["twoshot", "nvls", "oneshot", "auto"])
+ap.add_argument("--algo", default="auto", choices=["twoshot", "nvls", "oneshot", "auto"])
 a = ap.parse_args()
 rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
 torch.cuda.set_device(local)
@@ -32,19 +34,20 @@ g = torch.Generator().manual_seed(rank)
 x = torch.randn(B, 784, generator=g).to(torch.bfloat16).to(dev)
 y = torch.randint(0, 10, (B,), generator=g).to(dev)
 out = {"world": world, "per_gpu_batch": B, "grad_bytes_bf16": 20037642 * 2, "algo": a.algo}
+sampler = ClockSampler(local, period_s=0.02).start() if rank == 0 else None
 
 
 def timed(fn, steps, warm):
     for _ in range(warm): fn()
     torch.cuda.synchronize()
-    if world > 1: dist.barrier(); torch.cuda.synchronize()
+    if world > 1: comm.host_barrier(); torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(steps): fn()
     e1.record(); torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / steps
     if world > 1:
-        t = torch.tensor([ms], device=dev); dist.all_reduce(t, op=dist.ReduceOp.MAX); ms = float(t)
+        ms = comm.max_over_ranks(ms)
     return ms
 
 # ---- ours
@@ -88,7 +91,7 @@ if not a.skip_torch:
     torch.manual_seed(0)
     tm = nn.Sequential(nn.Linear(784, 4096), nn.ReLU(), nn.Linear(4096, 4096), nn.ReLU(), nn.Linear(4096, 10)).to(dev).to(torch.bfloat16)
     if world > 1:
-        tm = nn.parallel.DistributedDataParallel(tm, device_ids=[local])
+        tm = nn.parallel.DistributedDataParallel(tm, device_ids=[local], process_group=nccl_group())
     topt = torch.optim.SGD(tm.parameters(), lr=0.02, momentum=0.5)
     lossf = nn.CrossEntropyLoss()
     def torch_step():
@@ -100,6 +103,9 @@ for k in list(out):
     if k.endswith("_ms"):
         out[k.replace("_ms", "_img_per_s")] = round(B * world / (out[k] * 1e-3))
 if rank == 0:
+    out["clocks"] = sampler.stop()
     print(json.dumps(out, indent=1))
+    if os.environ.get("B200DP_OUT"):
+        Path(os.environ["B200DP_OUT"]).write_text(json.dumps(out, indent=1))
 if comm is not None:
     P.destroy_process_group()

@@ -8,6 +8,8 @@ import torch.distributed as dist
 from csed_514_project_distributed_training_using_pytorch_b200 import parallel as P
 from csed_514_project_distributed_training_using_pytorch_b200.models import Net
 from csed_514_project_distributed_training_using_pytorch_b200.parallel.data_parallel import DataParallel
+from csed_514_project_distributed_training_using_pytorch_b200.utils.clocks import ClockSampler
+from _nccl import nccl_group
 
 
 def timed(comm, fn, iters, warm=10):
@@ -30,6 +32,8 @@ def main():
     comm = P.init_process_group("b200", rank=rank, world_size=world)
     dev = comm.device
     out = {"world": world}
+    sampler = ClockSampler(local, period_s=0.02).start() if rank == 0 else None
+    ng = nccl_group()
     what = sys.argv[1] if len(sys.argv) > 1 else "net"
     if what in ("net", "all"):
         torch.manual_seed(1)
@@ -77,7 +81,7 @@ def main():
                 tn = globals()["nv"][:n]
                 row["nvls_us"] = timed(comm, lambda: comm.all_reduce(tn, "sum", "nvls"), iters)
             x = torch.randn(n, device=dev)
-            row["nccl_us"] = timed(comm, lambda: dist.all_reduce(x), iters)
+            row["nccl_us"] = timed(comm, lambda: dist.all_reduce(x, group=ng), iters)
             for k in ("oneshot_us", "twoshot_us", "nvls_us", "nccl_us"):
                 if k in row:   # bus bandwidth = 2(N-1)/N * S / t
                     row[k.replace("_us", "_busGBs")] = 2 * (world - 1) / world * nbytes / (row[k] * 1e-6) / 1e9
@@ -119,9 +123,12 @@ def main():
             g = ddp.flat.grad[lo:hi]
             out[f"bucket{b}_plain_twoshot_us"] = timed(comm, lambda: comm.all_reduce(g, "mean", "twoshot"), 50)
             xx = torch.randn(hi - lo, device=dev).to(torch.bfloat16)
-            out[f"bucket{b}_nccl_us"] = timed(comm, lambda: dist.all_reduce(xx), 50)
+            out[f"bucket{b}_nccl_us"] = timed(comm, lambda: dist.all_reduce(xx, group=ng), 50)
     if rank == 0:
+        out["clocks"] = sampler.stop()
         print(json.dumps(out, indent=1))
+        if os.environ.get("B200DP_OUT"):
+            Path(os.environ["B200DP_OUT"]).write_text(json.dumps(out, indent=1))
     P.destroy_process_group()
 
 
