@@ -29,6 +29,7 @@ def timed(comm, fn, iters, warm=10):
 def main():
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
+    os.environ.setdefault("B200DP_ARENA_MB", "2048")   # the sweep stages up to 64 MiB per source
     comm = P.init_process_group("b200", rank=rank, world_size=world)
     dev = comm.device
     out = {"world": world}

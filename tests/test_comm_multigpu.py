@@ -65,7 +65,7 @@ def test_net_ddp_persistent_multistep_peer(native_lib, tmp_path):
         assert (p["losses"] > 1.5).all() and (p["losses"] < 3.5).all()
 
 
-@pytest.mark.parametrize("algo", ["oneshot", "twoshot", "nvls"])
+@pytest.mark.parametrize("algo", ["oneshot", "twoshot", "nvls", "auto"])
 def test_mlp_ddp_peer(native_lib, tmp_path, algo):
     """bf16 MLP: replicas stay bit-identical; result tracks an fp32 single-process oracle."""
     from csed_514_project_distributed_training_using_pytorch_b200.models.mlp import WideMLP

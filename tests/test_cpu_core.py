@@ -255,4 +255,5 @@ def test_allreduce_algorithm_choice_includes_nvls():
     assert choose_from_table(8, 200 << 20, nvls_ok=True) == 1    # beyond the range NVLS won
     assert choose_from_table(2, 1 << 20, nvls_ok=True) == 0      # two ranks: one-shot up to 4 MiB
     assert choose_from_table(2, 32 << 20, nvls_ok=True) == 1     # NVLS never won on two ranks
-    assert choose_from_table(4, 2048) == 0                       # unmeasured world: nearest row
+    assert choose_from_table(4, 2 << 20, nvls_ok=True) == 2      # four ranks: NVLS at 1-4 MiB
+    assert choose_from_table(3, 2048) == 0                       # unmeasured world: nearest row
