@@ -41,6 +41,8 @@ _SIGS = {
     "b200_conv2_fwd": [c_p, c_p, c_p, c_p, c_i, c_f, c_ull, c_ull, c_p, c_p, c_i, c_p],
     "b200_conv2_fwd_tc": [c_p, c_p, c_p, c_p, c_i, c_f, c_ull, c_ull, c_p, c_p, c_i, c_p],
     "b200_a1_to_c4": [c_p, c_p, c_i, c_p],
+    "b200_conv2_w_to_operand": [c_p, c_p, c_p],
+    "b200_conv2_operand_floats": [],
     "b200_conv2_fwd_tc2": [c_p, c_p, c_p, c_p, c_i, c_f, c_ull, c_ull, c_p, c_p, c_i, c_p],
     "b200_conv2_bwd": [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_p],
     "b200_fc1_fwd": [c_p, c_p, c_p, c_p, c_i, c_f, c_ull, c_ull, c_p, c_i, c_p],

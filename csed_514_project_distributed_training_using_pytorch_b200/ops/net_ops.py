@@ -90,7 +90,9 @@ class Conv2DropPoolRelu(torch.autograd.Function):
         if impl == "tc":
             c4 = torch.empty(B, 4, 12, 12, 4, dtype=torch.float32, device=a1.device)
             N.call("b200_a1_to_c4", N.ptr(a1), N.ptr(c4), B, N.stream())
-            N.call("b200_conv2_fwd_tc2", N.ptr(c4), N.ptr(w), N.ptr(b), N.ptr(mask), mask_mode, float(p),
+            wop = torch.empty(N.lib().b200_conv2_operand_floats(), dtype=torch.float32, device=a1.device)
+            N.call("b200_conv2_w_to_operand", N.ptr(w), N.ptr(wop), N.stream())
+            N.call("b200_conv2_fwd_tc2", N.ptr(c4), N.ptr(wop), N.ptr(b), N.ptr(mask), mask_mode, float(p),
                    int(seed), int(step), N.ptr(a2), N.ptr(pos2), B, N.stream())
         else:
             N.call("b200_conv2_fwd_tc" if impl == "tcgen05" else "b200_conv2_fwd", N.ptr(a1), N.ptr(w),

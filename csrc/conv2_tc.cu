@@ -31,7 +31,8 @@ constexpr int A_BYTES = CHUNKS * A_CHUNK_BYTES;        // 18432
 constexpr int NPAD = 32;                               // 20 output channels padded
 constexpr int B_TAP_BYTES = CHUNKS * NPAD * 16;        // 2048
 constexpr int B_BYTES = 25 * B_TAP_BYTES;              // 51200
-constexpr int FWD_SMEM = A_BYTES + B_BYTES + 256 + 1024;
+constexpr int STAGES = 4;                              // A-tile ring depth
+constexpr int FWD_SMEM = STAGES * A_BYTES + B_BYTES + 256 + 1024;
 
 __device__ __forceinline__ uint32_t s32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -103,8 +104,35 @@ __global__ void a1_to_c4_kernel(const float* __restrict__ a1, float* __restrict_
   reinterpret_cast<float4*>(c4)[i] = make_float4(v[0], v[1], v[2], v[3]);
 }
 
+// ---- weights [20][10][5][5] -> B operand [tap 25][chunk 4][co 32][4 floats], zero padded ----------
+__global__ void conv2_w_to_operand_kernel(const float* __restrict__ w, float* __restrict__ wb) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;       // one float4 of the operand per thread
+  if (i >= 25 * CHUNKS * NPAD) return;
+  const int co = i % NPAD, ch = (i / NPAD) % CHUNKS, tap = i / (NPAD * CHUNKS);
+  float v[4];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const int ci = ch * 4 + q;
+    v[q] = (co < C2 && ci < C1) ? __ldg(w + (co * C1 + ci) * 25 + tap) : 0.0f;
+  }
+  reinterpret_cast<float4*>(wb)[i] = make_float4(v[0], v[1], v[2], v[3]);
+}
+
 // ---- forward ---------------------------------------------------------------------------------
-// One CTA = two images. mask_mode as in b200_conv2_fwd (0 none, 1 Philox + store, 2 given).
+// Persistent and warp-specialised: a CTA loops over image pairs with a two-deep pipeline.
+//   warp 4, one lane : TMA producer  (5-D load of the next pair into A[buf])
+//   warp 5, one lane : MMA issuer    (50 tcgen05.mma per pair into TMEM accumulator buf; one commit
+//                                      frees A[buf] for the producer, one hands the accumulator over)
+//   warps 0-3        : epilogue out of TMEM (bias, Dropout2d, pool + arg-max, ReLU, stores)
+// The weights are laid out once per CTA. mask_mode as in b200_conv2_fwd (0 none, 1 Philox + store,
+// 2 given).
+__device__ __forceinline__ void bar_init(uint64_t* b, uint32_t n) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(s32(b)), "r"(n));
+}
+__device__ __forceinline__ void bar_arrive(uint64_t* b) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(s32(b)) : "memory");
+}
+
 __global__ void __launch_bounds__(CT_THREADS, 1)
 conv2_fwd_tc2_kernel(const __grid_constant__ CUtensorMap map_a1, const float* __restrict__ w,
                      const float* __restrict__ b, float* __restrict__ mask, int mask_mode, float p,
@@ -112,115 +140,121 @@ conv2_fwd_tc2_kernel(const __grid_constant__ CUtensorMap map_a1, const float* __
                      uint8_t* __restrict__ pos2, int B) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  uint8_t* As = smem;                       // [chunk][Y][img][X][4 floats]
-  uint8_t* Bs = As + A_BYTES;               // [tap][chunk][co 32][4 floats]
-  uint64_t* bar_in = reinterpret_cast<uint64_t*>(Bs + B_BYTES);
-  uint64_t* bar_mma = bar_in + 1;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_mma + 1);
-  __shared__ float bias_s[NPAD], mask_s[2][NPAD];
+  uint8_t* As = smem;                       // [stage][chunk][Y][img][X][4 floats]
+  uint8_t* Bs = As + STAGES * A_BYTES;      // [tap][chunk][co 32][4 floats]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(Bs + B_BYTES);
+  uint64_t* a_full = bars;                  // [STAGES] TMA landed
+  uint64_t* a_free = bars + STAGES;         // [STAGES] the MMAs that read A[stage] are done
+  uint64_t* acc_full = bars + 2 * STAGES;   // [2] accumulator buf is complete
+  uint64_t* acc_free = acc_full + 2;        // [2] the epilogue has drained accumulator buf
+  uint64_t* w_full = acc_free + 2;          // the pre-laid-out weights have landed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(w_full + 1);
+  __shared__ float bias_s[NPAD];
   const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
-  const int img0 = blockIdx.x * 2;
-  const int nimg = min(2, B - img0);
+  const int npairs = (B + 1) / 2;
 
   if (t == 0) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(s32(bar_in)));
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(s32(bar_mma)));
+    for (int i = 0; i < STAGES; ++i) { bar_init(a_full + i, 1); bar_init(a_free + i, 1); }
+    for (int i = 0; i < 2; ++i) { bar_init(acc_full + i, 1); bar_init(acc_free + i, 4); }
+    bar_init(w_full, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 32;" ::"r"(s32(tmem_slot)) : "memory");
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 64;" ::"r"(s32(tmem_slot)) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
   if (t < NPAD) bias_s[t] = (t < C2) ? b[t] : 0.0f;
-  if (t < 2 * NPAD) {
-    const int im = t / NPAD, co = t % NPAD;
-    float m = 1.0f;
-    if (co < C2 && im < nimg) {
-      if (mask_mode == 1) {
-        m = dropout_mask_value(seed, step, (uint32_t)(img0 + im), 0x20000u + co, p);
-        mask[(size_t)(img0 + im) * C2 + co] = m;
-      } else if (mask_mode == 2) {
-        m = mask[(size_t)(img0 + im) * C2 + co];
-      }
-    }
-    mask_s[im][co] = m;
-  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem = *tmem_slot;
 
-  // 1. one 5-D TMA load: box (4 floats, X 12, image 2, Y 12, chunk 4) -> As; images beyond B are
-  //    zero-filled by the tensor map's bounds
-  if (t == 0) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(s32(bar_in)), "r"((uint32_t)A_BYTES) : "memory");
-    asm volatile(
-        "cp.async.bulk.tensor.5d.shared::cluster.global.mbarrier::complete_tx::bytes"
-        " [%0], [%1, {%3, %4, %5, %6, %7}], [%2];" ::"r"(s32(As)),
-        "l"(&map_a1), "r"(s32(bar_in)), "r"(0), "r"(0), "r"(img0), "r"(0), "r"(0)
-        : "memory");
-  }
-  // 2. weights -> B operand [tap][chunk][co][4]: element (tap, ci, co) = W2[co][ci][tap]
-  for (int i = t; i < 25 * CHUNKS * NPAD; i += CT_THREADS) {
-    const int co = i % NPAD, ch = (i / NPAD) % CHUNKS, tap = i / (NPAD * CHUNKS);
-    float v[4];
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      const int ci = ch * 4 + q;
-      v[q] = (co < C2 && ci < C1) ? __ldg(w + (co * C1 + ci) * 25 + tap) : 0.0f;
+  if (warp == 4 && lane == 0) {
+    // ---------------- TMA producer: the weights (already in operand layout, one 51 KB bulk copy)
+    // and then the ring of activation tiles
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(s32(w_full)), "r"((uint32_t)B_BYTES) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(s32(Bs)),
+                 "l"(w), "r"((uint32_t)B_BYTES), "r"(s32(w_full)) : "memory");
+    int it = 0;
+    for (int pair = blockIdx.x; pair < npairs; pair += gridDim.x, ++it) {
+      const int buf = it % STAGES;
+      if (it >= STAGES) bar_wait(a_free + buf, ((it / STAGES) - 1) & 1);
+      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(s32(a_full + buf)), "r"((uint32_t)A_BYTES) : "memory");
+      asm volatile(
+          "cp.async.bulk.tensor.5d.shared::cluster.global.mbarrier::complete_tx::bytes"
+          " [%0], [%1, {%3, %4, %5, %6, %7}], [%2];" ::"r"(s32(As + buf * A_BYTES)),
+          "l"(&map_a1), "r"(s32(a_full + buf)), "r"(0), "r"(0), "r"(2 * pair), "r"(0), "r"(0)
+          : "memory");
     }
-    reinterpret_cast<float4*>(Bs)[i] = make_float4(v[0], v[1], v[2], v[3]);
-  }
-  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-  __syncthreads();
-
-  // 3. 50 MMAs: only the start addresses move
-  if (warp == 0 && lane == 0) {
-    bar_wait(bar_in, 0);
-    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  } else if (warp == 5 && lane == 0) {
+    // ---------------- MMA issuer: only the start addresses move with the tap
     constexpr uint32_t idesc = idesc_tf32(128, NPAD);
-    const uint32_t a0 = s32(As), b0 = s32(Bs);
-    uint32_t acc = 0;
+    const uint32_t b0 = s32(Bs);
+    bar_wait(w_full, 0);
+    int it = 0;
+    for (int pair = blockIdx.x; pair < npairs; pair += gridDim.x, ++it) {
+      const int buf = it & 1, st = it % STAGES;
+      if (it >= 2) bar_wait(acc_free + buf, ((it >> 1) - 1) & 1);
+      bar_wait(a_full + st, (it / STAGES) & 1);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      const uint32_t a0 = s32(As + st * A_BYTES);
+      uint32_t acc = 0;
 #pragma unroll 1
-    for (int tap = 0; tap < 25; ++tap) {
-      const int ky = tap / 5, kx = tap - ky * 5;
+      for (int tap = 0; tap < 25; ++tap) {
+        const int ky = tap / 5, kx = tap - ky * 5;
 #pragma unroll
-      for (int kc = 0; kc < 2; ++kc) {
-        const uint64_t ad = desc_k_noswz(a0 + (2 * kc) * A_CHUNK_BYTES + (ky * 24 + kx) * 16,
-                                         A_CHUNK_BYTES, 12 * 16);
-        const uint64_t bd = desc_k_noswz(b0 + tap * B_TAP_BYTES + (2 * kc) * (NPAD * 16), NPAD * 16, 128);
-        mma_tf32(tmem, ad, bd, idesc, acc);
-        acc = 1;
+        for (int kc = 0; kc < 2; ++kc) {
+          const uint64_t ad = desc_k_noswz(a0 + (2 * kc) * A_CHUNK_BYTES + (ky * 24 + kx) * 16, A_CHUNK_BYTES, 12 * 16);
+          const uint64_t bd = desc_k_noswz(b0 + tap * B_TAP_BYTES + (2 * kc) * (NPAD * 16), NPAD * 16, 128);
+          mma_tf32(tmem + buf * NPAD, ad, bd, idesc, acc);
+          acc = 1;
+        }
       }
+      mma_commit(a_free + st);
+      mma_commit(acc_full + buf);
     }
-    mma_commit(bar_mma);
-  }
-
-  // 4. epilogue out of TMEM: lane l of warp w holds GEMM row 32w + l = (g = 4w + l/8, x = l%8),
-  //    g = 2*y + image. The 2x2 window (py = w, px = x/2) of an image is lanes l, l^1, l^16, l^17.
-  if (warp < 4) {
-    bar_wait(bar_mma, 0);
-    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    uint32_t r[32];
-    tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16), r);
+  } else if (warp < 4) {
+    // ---------------- epilogue: lane l of warp w holds GEMM row 32w + l = (g = 4w + l/8, x = l%8),
+    // g = 2*y + image. The 2x2 window (py = w, px = x/2) of an image is lanes l, l^1, l^16, l^17.
     const int gl = lane >> 3, x = lane & 7;
     const int im = gl & 1, dy0 = gl >> 1, dx0 = x & 1;
     const int py = warp, px = x >> 1;
     const int j = dy0 * 2 + dx0;                 // scan order inside the window
+    int it = 0;
+    for (int pair = blockIdx.x; pair < npairs; pair += gridDim.x, ++it) {
+      const int buf = it & 1;
+      const int img = 2 * pair + im;
+      bar_wait(acc_full + buf, (it >> 1) & 1);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      uint32_t r[32];
+      tmem_ld32(tmem + buf * NPAD + ((uint32_t)(warp * 32) << 16), r);
+      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) bar_arrive(acc_free + buf);   // the accumulator may be overwritten now
+      const bool writer = (j == 0) && img < B;
 #pragma unroll
-    for (int co = 0; co < C2; ++co) {
-      float v = __uint_as_float(r[co]) + bias_s[co];
-      int jj = j;
+      for (int co = 0; co < C2; ++co) {
+        float v = __uint_as_float(r[co]) + bias_s[co];
+        int jj = j;
 #pragma unroll
-      for (int o = 1; o <= 16; o <<= 4) {        // partners l^1, then l^16
-        const float ov = __shfl_xor_sync(0xffffffffu, v, o);
-        const int oj = __shfl_xor_sync(0xffffffffu, jj, o);
-        if (ov > v || (ov == v && oj < jj)) { v = ov; jj = oj; }   // first max in scan order
-      }
-      if (j == 0 && im < nimg) {
-        const size_t o = (size_t)(img0 + im) * A2_SZ + co * 16 + py * 4 + px;
-        a2[o] = fmaxf(v * mask_s[im][co], 0.0f);
-        pos2[o] = (uint8_t)((2 * py + (jj >> 1)) * 12 + 2 * px + (jj & 1));
+        for (int o = 1; o <= 16; o <<= 4) {        // partners l^1, then l^16
+          const float ov = __shfl_xor_sync(0xffffffffu, v, o);
+          const int oj = __shfl_xor_sync(0xffffffffu, jj, o);
+          if (ov > v || (ov == v && oj < jj)) { v = ov; jj = oj; }   // first max in scan order
+        }
+        if (writer) {
+          float m = 1.0f;
+          if (mask_mode == 1) {
+            m = dropout_mask_value(seed, step, (uint32_t)img, 0x20000u + co, p);
+            if (py == 0 && px == 0) mask[(size_t)img * C2 + co] = m;
+          } else if (mask_mode == 2) {
+            m = __ldg(mask + (size_t)img * C2 + co);
+          }
+          const size_t o = (size_t)img * A2_SZ + co * 16 + py * 4 + px;
+          a2[o] = fmaxf(v * m, 0.0f);
+          pos2[o] = (uint8_t)((2 * py + (jj >> 1)) * 12 + 2 * px + (jj & 1));
+        }
       }
     }
   }
@@ -228,7 +262,7 @@ conv2_fwd_tc2_kernel(const __grid_constant__ CUtensorMap map_a1, const float* __
   __syncthreads();
   if (warp == 1) {
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 32;" ::"r"(tmem) : "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 64;" ::"r"(tmem) : "memory");
   }
 }
 
@@ -279,13 +313,24 @@ int b200_a1_to_c4(const float* a1, float* c4, int B, void* stream) {
   return 0;
 }
 
-// conv2 forward + bias + Dropout2d + 2x2 max-pool + ReLU from c4 activations; same outputs as
-// b200_conv2_fwd. Ref: src/model.py:17.
+// conv2.weight [20][10][5][5] -> the tensor-core B operand [25 taps][4 chunks][32][4] (12,800
+// floats, zero padded). Once per weight update.
+int b200_conv2_w_to_operand(const float* w, float* w_operand, void* stream) {
+  const int n = 25 * CHUNKS * NPAD;
+  conv2_w_to_operand_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(w, w_operand);
+  B200_LAUNCH_OK();
+  return 0;
+}
+int b200_conv2_operand_floats(void) { return B_BYTES / 4; }
+
+// conv2 forward + bias + Dropout2d + 2x2 max-pool + ReLU from c4 activations and the weight
+// operand of b200_conv2_w_to_operand; same outputs as b200_conv2_fwd. Ref: src/model.py:17.
 int b200_conv2_fwd_tc2(const float* a1_c4, const float* w, const float* b, float* mask, int mask_mode,
                        float p, unsigned long long seed, unsigned long long step, float* a2,
                        void* pos2, int B, void* stream) {
   if (B <= 0) return 0;
   B200_REQUIRE(mask_mode == 0 || mask != nullptr, "b200_conv2_fwd_tc2: mask buffer required");
+  B200_REQUIRE(((uintptr_t)w & 15) == 0, "b200_conv2_fwd_tc2: the weight operand must be 16-byte aligned");
   static bool attr_done[64] = {false};
   int dev = 0;
   B200_CUDA_OK(cudaGetDevice(&dev));
@@ -295,7 +340,8 @@ int b200_conv2_fwd_tc2(const float* a1_c4, const float* w, const float* b, float
   }
   CUtensorMap map;
   if (int e = make_c4_map(&map, a1_c4, B)) return e;
-  conv2_fwd_tc2_kernel<<<(B + 1) / 2, CT_THREADS, FWD_SMEM, (cudaStream_t)stream>>>(
+  const int npairs = (B + 1) / 2;
+  conv2_fwd_tc2_kernel<<<npairs < 148 ? npairs : 148, CT_THREADS, FWD_SMEM, (cudaStream_t)stream>>>(
       map, w, b, mask, mask_mode, p, seed, step, a2, (uint8_t*)pos2, B);
   B200_LAUNCH_OK();
   return 0;

@@ -207,7 +207,11 @@ int b200_conv2_fwd_tc(const float* a1, const float* w, const float* b, float* ma
  * a descriptor start-address shift, 50 tcgen05.mma.kind::tf32 per pair, pool/ReLU/Dropout2d in the
  * TMEM epilogue. Same outputs as b200_conv2_fwd. Ref: src/model.py:17 */
 int b200_a1_to_c4(const float* a1, float* c4, int B, void* stream);
-int b200_conv2_fwd_tc2(const float* a1_c4, const float* w, const float* b, float* mask, int mask_mode,
+/* conv2.weight -> tensor-core B operand [25 taps][4 chunks][32][4 floats] (b200_conv2_operand_floats()
+ * floats); b200_conv2_fwd_tc2 takes THAT as `w_operand`. */
+int b200_conv2_w_to_operand(const float* w, float* w_operand, void* stream);
+int b200_conv2_operand_floats(void);
+int b200_conv2_fwd_tc2(const float* a1_c4, const float* w_operand, const float* b, float* mask, int mask_mode,
                        float p, unsigned long long seed, unsigned long long step, float* a2,
                        void* pos2, int B, void* stream);
 /* MLP helpers: fused softmax + NLL + gradient, bias gradient, master-weight SGD. */
