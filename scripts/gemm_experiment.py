@@ -4,7 +4,9 @@ import json, sys
 from pathlib import Path
 sys.path.insert(0, str(Path(__file__).resolve().parents[1]))
 import torch
+import os
 from csed_514_project_distributed_training_using_pytorch_b200.ops import gemm
+from csed_514_project_distributed_training_using_pytorch_b200.utils.clocks import ClockSampler
 
 
 def t(fn, iters=20, warm=4):
@@ -25,6 +27,7 @@ shapes = [(4096, 4096, 4096), (8192, 8192, 4096), (512, 4096, 4096), (4096, 4096
 if len(sys.argv) > 1:
     variants = [v for v in variants if v[0] in sys.argv[1].split(",")]
 rows = []
+sampler = ClockSampler(0, period_s=0.02).start()
 for (M, N, K) in shapes:
     x = torch.randn(M, K, device=dev).to(torch.bfloat16)
     W = torch.randn(N, K, device=dev).to(torch.bfloat16)
@@ -50,3 +53,9 @@ for (M, N, K) in shapes:
     gemm.set_variant("auto")
     rows.append(r)
     print(json.dumps(r), flush=True)
+clocks = sampler.stop()
+print(json.dumps({"clocks": clocks}), flush=True)
+if os.environ.get("B200DP_OUT"):
+    Path(os.environ["B200DP_OUT"]).write_text(json.dumps({"rows": rows, "clocks": clocks,
+        "unit": "TFLOP/s bf16, CUDA events over 20 back-to-back calls after 4 warm-up calls",
+        "columns": "_kk = both operands K-major, _mm = both MN-major, _err = max abs error / max |ref|"}, indent=1))

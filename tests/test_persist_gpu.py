@@ -221,3 +221,38 @@ def test_persist_plan_host_query(native_lib):
     assert p["split"] == 0 and p["workers"] == 100 and p["images_per_worker"] == 1
     p = persist_plan(512)
     assert p["workers"] == 128 and p["images_per_worker"] == 4 and p["grid"] <= 148
+
+
+def test_hundred_step_loss_curve_follows_oracle(cuda_device):
+    """100 optimizer steps on a learnable 10-template set, explicit dropout masks: the loss
+    curve of the persistent kernel stays on the fp64 oracle's (the loop
+    being pinned is src/train.py:66-76), and both curves go down."""
+    B, steps = 64, 100
+    g = torch.Generator().manual_seed(3)
+    templates = torch.randn(10, 784, generator=g)
+    net = _net(cuda_device, seed=4).train()
+    ref = _oracle_params(net)
+    eng = PersistentNetEngine(net, lr=0.02, momentum=0.5)
+    bufs = [torch.zeros_like(p) for p in ref]
+    ours, theirs = [], []
+    for it in range(steps):
+        y = torch.randint(0, 10, (B,), generator=g)
+        x = (templates[y] + 0.5 * torch.randn(B, 784, generator=g)).view(B, 1, 28, 28)
+        m2, m3 = oracle.make_masks(B, torch.Generator().manual_seed(100 + it))
+        eng.run_steps(x.to(cuda_device).view(B, 784), y.to(cuda_device), X_F32, batch=B, nsteps=1,
+                      masks=(m2.to(cuda_device), m3.to(cuda_device)))
+        for p in ref:
+            p.grad = None
+        lo = oracle.net_loss(ref, x.double(), y, m2.double(), m3.double())
+        lo.backward()
+        oracle.sgd_momentum_step(ref, [q.grad for q in ref], bufs, 0.02, 0.5)
+        theirs.append(float(lo))
+    torch.cuda.synchronize()
+    eng.check_errors()
+    ours = eng.last_losses(steps).tolist()
+    worst = max(abs(a - b) / max(abs(b), 1e-3) for a, b in zip(ours, theirs))
+    assert worst < 2e-3, f"loss curves part by {worst:.2e}: {ours[-3:]} vs {theirs[-3:]}"
+    assert sum(theirs[-10:]) / 10 < 0.5 * sum(theirs[:10]) / 10
+    for name, p, q in zip(Net.PARAM_ORDER, net.param_list(), ref):
+        torch.testing.assert_close(p.detach().cpu(), q.detach().float(), rtol=5e-3, atol=2e-4,
+                                   msg=lambda m, n=name: f"param {n} after {steps} steps: {m}")
