@@ -43,6 +43,16 @@ _SIGS = {
     "b200_a1_to_c4": [c_p, c_p, c_i, c_p],
     "b200_conv2_w_to_operand": [c_p, c_p, c_p],
     "b200_conv2_operand_floats": [],
+    "b200_conv2_frame_floats": [c_i],
+    "b200_conv2_dgrad_operand_floats": [],
+    "b200_conv2_dz_frame": [c_p, c_p, c_p, c_p, c_p, c_i, c_p],
+    "b200_conv2_w_to_dgrad_operand": [c_p, c_p, c_p],
+    "b200_conv2_dgrad_tc": [c_p, c_p, c_p, c_i, c_p],
+    "b200_conv2_wgrad_tc": [c_p, c_p, c_p, c_p, c_i, c_p],
+    "b200_conv2_c32_a1_floats": [c_i],
+    "b200_conv2_c32_dz_floats": [c_i],
+    "b200_a1_to_c32": [c_p, c_p, c_i, c_p],
+    "b200_conv2_dz_c32": [c_p, c_p, c_p, c_p, c_p, c_i, c_p],
     "b200_conv2_fwd_tc2": [c_p, c_p, c_p, c_p, c_i, c_f, c_ull, c_ull, c_p, c_p, c_i, c_p],
     "b200_conv2_bwd": [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_p],
     "b200_fc1_fwd": [c_p, c_p, c_p, c_p, c_i, c_f, c_ull, c_ull, c_p, c_i, c_p],

@@ -98,6 +98,7 @@ class Conv2DropPoolRelu(torch.autograd.Function):
             N.call("b200_conv2_fwd_tc" if impl == "tcgen05" else "b200_conv2_fwd", N.ptr(a1), N.ptr(w),
                    N.ptr(b), N.ptr(mask), mask_mode, float(p),
                    int(seed), int(step), N.ptr(a2), N.ptr(pos2), B, N.stream())
+        ctx.tc = impl == "tc"
         ctx.save_for_backward(a1, w, a2, pos2, mask if mask_mode else None)
         return a2
 
@@ -105,6 +106,8 @@ class Conv2DropPoolRelu(torch.autograd.Function):
     def backward(ctx, da2):
         a1, w, a2, pos2, mask = ctx.saved_tensors
         B = a1.shape[0]
+        if ctx.tc:
+            return Conv2DropPoolRelu._backward_tc(ctx, a1, w, a2, pos2, mask, _c(da2)) + (None,) * 6
         ws = workspace(a1.device)
         dw = torch.empty_like(w)
         db = torch.empty(20, dtype=torch.float32, device=a1.device)
@@ -113,6 +116,40 @@ class Conv2DropPoolRelu(torch.autograd.Function):
                N.ptr(mask), N.ptr(dw), N.ptr(db), N.ptr(da1), N.ptr(ws.scratch),
                N.ptr(ws.counter), B, N.stream())
         return da1, dw, db, None, None, None, None, None, None
+
+
+def _conv2_backward_tc(ctx, a1, w, a2, pos2, mask, da2):
+    """conv2 backward on tcgen05 (csrc/conv2_tc.cu): the weight/bias gradient as a pixel-reduction
+    GEMM with MN-major operands in a swizzled [pixel][32 channels] layout, the data gradient as
+    an implicit GEMM over a zero-padded dZ frame."""
+    B, dev, lib = a2.shape[0], a2.device, N.lib()
+    c32 = torch.empty(lib.b200_conv2_c32_a1_floats(B), dtype=torch.float32, device=dev)
+    dz32 = torch.empty(lib.b200_conv2_c32_dz_floats(B), dtype=torch.float32, device=dev)
+    N.call("b200_a1_to_c32", N.ptr(a1), N.ptr(c32), B, N.stream())
+    N.call("b200_conv2_dz_c32", N.ptr(da2), N.ptr(a2), N.ptr(pos2), N.ptr(mask), N.ptr(dz32), B, N.stream())
+    dw = torch.empty_like(w)
+    db = torch.empty(20, dtype=torch.float32, device=dev)
+    N.call("b200_conv2_wgrad_tc", N.ptr(c32), N.ptr(dz32), N.ptr(dw), N.ptr(db), B, N.stream())
+    da1 = None
+    if ctx.needs_input_grad[0]:
+        frame = torch.empty(lib.b200_conv2_frame_floats(B), dtype=torch.float32, device=dev)
+        N.call("b200_conv2_dz_frame", N.ptr(da2), N.ptr(a2), N.ptr(pos2), N.ptr(mask), N.ptr(frame), B, N.stream())
+        wd = torch.empty(lib.b200_conv2_dgrad_operand_floats(), dtype=torch.float32, device=dev)
+        N.call("b200_conv2_w_to_dgrad_operand", N.ptr(w), N.ptr(wd), N.stream())
+        da1 = torch.empty(B, 10, 12, 12, dtype=torch.float32, device=dev)
+        N.call("b200_conv2_dgrad_tc", N.ptr(frame), N.ptr(wd), N.ptr(da1), B, N.stream())
+    return da1, dw, db
+
+
+Conv2DropPoolRelu._backward_tc = staticmethod(_conv2_backward_tc)
+
+
+def conv2_backward_tc(a1, w, a2, pos2, mask, da2, need_da1: bool = True):
+    """(da1, dw, db) of conv2 + Dropout2d + pool + ReLU on the tensor cores, from the layer's
+    saved forward state (a2 and arg-max positions pos2 of either forward kernel)."""
+    class _Ctx:
+        needs_input_grad = (need_da1,)
+    return _conv2_backward_tc(_Ctx, _c(a1), _c(w), _c(a2), _c(pos2), mask, _c(da2))
 
 
 class Fc1ReluDrop(torch.autograd.Function):

@@ -266,6 +266,339 @@ conv2_fwd_tc2_kernel(const __grid_constant__ CUtensorMap map_a1, const float* __
   }
 }
 
+// =============================================================================================
+// Backward. The gradient before pooling, dZ [image][20][8][8], is nonzero at one position per
+// pooling window. It is written into a zero-padded FRAME per image and 4-channel chunk:
+//     frame pixel f = 4 + (y + 4) * 12 + x          (pitch 12, four zero rows above and below,
+//                                                    x = 8..11 zero, 200 pixels per plane)
+// The data gradient reads it with nothing but descriptor arithmetic:
+//   da1[q = Y*12 + X][ci] = sum over taps t' = (ky', kx') and co of
+//                           frame[q + ky'*12 + kx'][co] * Wflip[t'][co][ci]
+//   an implicit GEMM like the forward: A = frame, K-major, rows are consecutive frame pixels
+//   (SBO = 128 B); the four zero columns of a row are at once its right margin and the next
+//   row's left margin; M = 144 rows per image in two tiles of 128.
+// The weight gradient (further down) reduces over pixels and uses its own MN-major layout.
+constexpr int FRAME = 200;                              // pixels per chunk plane of the dZ frame
+constexpr int DZ_CHUNKS = 6;                            // 20 channels padded to 24
+constexpr int DZ_PLANE_BYTES = FRAME * 16;              // 3200
+constexpr int DZ_IMG_BYTES = DZ_CHUNKS * DZ_PLANE_BYTES;   // 19200
+constexpr int DZ_ORIGIN = 4 + 4 * 12;                   // frame pixel of (y, x) = (0, 0): 52
+constexpr int CIPAD = 16;                               // 10 input channels padded
+constexpr int WD_TAP_BYTES = DZ_CHUNKS * CIPAD * 16;    // 1536
+constexpr int WD_BYTES = 25 * WD_TAP_BYTES;             // 38400
+constexpr int DG_STAGES = 3;
+constexpr int DG_SMEM = DG_STAGES * DZ_IMG_BYTES + WD_BYTES + 256 + 1024;
+// dZ frame [B][6][200][4] from the pooled gradient: one float4 (pixel, chunk) per thread.
+__global__ void conv2_dz_frame_kernel(const float* __restrict__ da2, const float* __restrict__ a2,
+                                      const uint8_t* __restrict__ pos2, const float* __restrict__ mask,
+                                      float* __restrict__ frame, int B) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B * DZ_CHUNKS * FRAME) return;
+  const int f = i % FRAME, ch = (i / FRAME) % DZ_CHUNKS, img = i / (FRAME * DZ_CHUNKS);
+  float v[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+  const int q = f - DZ_ORIGIN;                     // y*12 + x of the pre-pool position
+  if (q >= 0 && ch < 5) {
+    const int y = q / 12, x = q - y * 12;
+    if (y < 8 && x < 8) {
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        const int co = ch * 4 + c;
+        const size_t gi = (size_t)img * A2_SZ + co * 16 + (y >> 1) * 4 + (x >> 1);
+        if (pos2[gi] == q && a2[gi] > 0.0f)
+          v[c] = da2[gi] * (mask ? mask[(size_t)img * C2 + co] : 1.0f);
+      }
+    }
+  }
+  reinterpret_cast<float4*>(frame)[i] = make_float4(v[0], v[1], v[2], v[3]);
+}
+
+// weights [20][10][5][5] -> data-gradient B operand [tap' 25][chunk 6][ci 16][4 co], flipped taps
+__global__ void conv2_w_to_dgrad_operand_kernel(const float* __restrict__ w, float* __restrict__ wd) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= 25 * DZ_CHUNKS * CIPAD) return;
+  const int ci = i % CIPAD, ch = (i / CIPAD) % DZ_CHUNKS, tp = i / (CIPAD * DZ_CHUNKS);
+  const int tap = 24 - tp;                         // (4 - ky') * 5 + (4 - kx')
+  float v[4];
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    const int co = ch * 4 + c;
+    v[c] = (co < C2 && ci < C1) ? __ldg(w + (co * C1 + ci) * 25 + tap) : 0.0f;
+  }
+  reinterpret_cast<float4*>(wd)[i] = make_float4(v[0], v[1], v[2], v[3]);
+}
+
+__device__ __forceinline__ void bulk_load(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(s32(dst)),
+               "l"(src), "r"(bytes), "r"(s32(bar)) : "memory");
+}
+__device__ __forceinline__ void bar_expect(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(s32(bar)), "r"(bytes) : "memory");
+}
+
+// ---- data gradient -----------------------------------------------------------------------------
+// Persistent, one image per pipeline stage. warp 4 lane 0: bulk copies (the flipped weights once,
+// then one 19,200-byte dZ frame per image); warp 5 lane 0: 2 tiles x 25 taps x 3 K-steps of
+// tcgen05.mma.kind::tf32 (M=128, N=16, K=8); warps 0-3: TMEM -> da1 [B][10][12][12].
+__global__ void __launch_bounds__(CT_THREADS, 1)
+conv2_dgrad_tc_kernel(const float* __restrict__ frame, const float* __restrict__ wd,
+                      float* __restrict__ da1, int B) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* As = smem;                              // [stage][chunk 6][200 pixels][4 floats]
+  uint8_t* Bs = As + DG_STAGES * DZ_IMG_BYTES;     // [tap'][chunk 6][ci 16][4 floats]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(Bs + WD_BYTES);
+  uint64_t* a_full = bars;
+  uint64_t* a_free = bars + DG_STAGES;
+  uint64_t* acc_full = bars + 2 * DG_STAGES;
+  uint64_t* acc_free = acc_full + 2;
+  uint64_t* w_full = acc_free + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(w_full + 1);
+  const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+
+  if (t == 0) {
+    for (int i = 0; i < DG_STAGES; ++i) { bar_init(a_full + i, 1); bar_init(a_free + i, 1); }
+    for (int i = 0; i < 2; ++i) { bar_init(acc_full + i, 1); bar_init(acc_free + i, 4); }
+    bar_init(w_full, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 64;" ::"r"(s32(tmem_slot)) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp == 4 && lane == 0) {
+    bar_expect(w_full, WD_BYTES);
+    bulk_load(Bs, wd, WD_BYTES, w_full);
+    int it = 0;
+    for (int img = blockIdx.x; img < B; img += gridDim.x, ++it) {
+      const int st = it % DG_STAGES;
+      if (it >= DG_STAGES) bar_wait(a_free + st, ((it / DG_STAGES) - 1) & 1);
+      bar_expect(a_full + st, DZ_IMG_BYTES);
+      bulk_load(As + st * DZ_IMG_BYTES, frame + (size_t)img * (DZ_IMG_BYTES / 4), DZ_IMG_BYTES, a_full + st);
+    }
+  } else if (warp == 5 && lane == 0) {
+    constexpr uint32_t idesc = idesc_tf32(128, CIPAD);
+    const uint32_t b0 = s32(Bs);
+    bar_wait(w_full, 0);
+    int it = 0;
+    for (int img = blockIdx.x; img < B; img += gridDim.x, ++it) {
+      const int buf = it & 1, st = it % DG_STAGES;
+      if (it >= 2) bar_wait(acc_free + buf, ((it >> 1) - 1) & 1);
+      bar_wait(a_full + st, (it / DG_STAGES) & 1);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      const uint32_t a0 = s32(As + st * DZ_IMG_BYTES);
+#pragma unroll 1
+      for (int tile = 0; tile < 2; ++tile) {
+        uint32_t acc = 0;
+#pragma unroll 1
+        for (int tp = 0; tp < 25; ++tp) {
+          const int ky = tp / 5, kx = tp - ky * 5;
+          const uint32_t arow = a0 + (uint32_t)(tile * 128 + ky * 12 + kx) * 16;
+#pragma unroll
+          for (int kc = 0; kc < 3; ++kc) {
+            const uint64_t ad = desc_k_noswz(arow + (2 * kc) * DZ_PLANE_BYTES, DZ_PLANE_BYTES, 128);
+            const uint64_t bd = desc_k_noswz(b0 + tp * WD_TAP_BYTES + (2 * kc) * (CIPAD * 16), CIPAD * 16, 128);
+            mma_tf32(tmem + (buf * 2 + tile) * CIPAD, ad, bd, idesc, acc);
+            acc = 1;
+          }
+        }
+      }
+      mma_commit(a_free + st);
+      mma_commit(acc_full + buf);
+    }
+  } else if (warp < 4) {
+    // lane l of warp w: row 32w + l of tile 0 (columns 0..15) and of tile 1 (columns 16..31)
+    int it = 0;
+    for (int img = blockIdx.x; img < B; img += gridDim.x, ++it) {
+      const int buf = it & 1;
+      bar_wait(acc_full + buf, (it >> 1) & 1);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      uint32_t r[32];
+      tmem_ld32(tmem + buf * 2 * CIPAD + ((uint32_t)(warp * 32) << 16), r);
+      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) bar_arrive(acc_free + buf);
+      float* out = da1 + (size_t)img * A1_SZ;
+      const int q0 = warp * 32 + lane, q1 = 128 + q0;
+#pragma unroll
+      for (int ci = 0; ci < C1; ++ci) {
+        out[ci * 144 + q0] = __uint_as_float(r[ci]);
+        if (q1 < 144) out[ci * 144 + q1] = __uint_as_float(r[CIPAD + ci]);
+      }
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 64;" ::"r"(tmem) : "memory");
+  }
+}
+
+// ---- weight (and bias) gradient ----------------------------------------------------------------
+// The reduction runs over pixels, so both operands are MN-major. For TF32 the tensor core reads
+// MN-major operands in one layout only (measured, scripts/experiments/umma_mn_probe.cu: every
+// other layout type returns zeros): layout type 1, "128-byte swizzle with 32-byte atoms":
+//     a K row (= pixel) is 128 bytes = 32 channels; 4 K rows per group, groups SBO apart;
+//     the next 32 M/N elements are LBO away; 32-byte unit u of K row r sits at u ^ (r & 3),
+//     taken from the ABSOLUTE shared-memory address (bits 5-6 ^= bits 7-8).
+// Both operands therefore use a "c32" layout, [pixel][32 channels], written pre-swizzled in
+// global memory so that plain bulk copies into 512-byte aligned tiles keep the pattern:
+//     A = a1  [160 pixels][32]: channels 0..9, channel 10 = 1 (its tap-0 gradient is the bias
+//             gradient), rest 0; pixels 144..159 zero
+//     B = dZ  [96 pixels][32]:  pitch-12 rows y = 0..7, x = 8..11 zero, channels 20..31 zero
+// A's LBO is ONE pixel row: the four 32-channel groups of M = 128 are four consecutive shifts
+// j0..j0+3 of the image, so one MMA yields dW[:, :, ky, kx..kx+3] (j0 = ky*12 + kx); ten
+// accumulators (5 filter rows x {kx 0..3, kx 4}) cover the filter. Per image: 12 K-steps of 8
+// pixels x 10 tcgen05.mma (M=128, N=32, K=8). The CTAs' sums meet in fp32 atomics.
+constexpr int C32_A1_PIX = 160;
+constexpr int C32_A1_BYTES = C32_A1_PIX * 128;          // 20480
+constexpr int C32_DZ_PIX = 96;
+constexpr int C32_DZ_BYTES = C32_DZ_PIX * 128;          // 12288
+constexpr int WG_STAGE_BYTES = C32_A1_BYTES + C32_DZ_BYTES;   // 32768
+constexpr int WG_STAGES = 4;
+constexpr int WG_SMEM = WG_STAGES * WG_STAGE_BYTES + 256 + 1024;
+
+__device__ __forceinline__ uint64_t desc_mn_sw32atom(uint32_t addr, uint32_t lbo, uint32_t sbo) {
+  return desc_k_noswz(addr, lbo, sbo) | ((uint64_t)1 << 61);    // layout type 1
+}
+constexpr uint32_t idesc_tf32_mn(int M, int N) {        // both operands MN-major
+  return idesc_tf32(M, N) | (1u << 15) | (1u << 16);
+}
+
+// a1 [B][10][12][12] -> swizzled c32 [B][160][32]; one 32-byte unit per thread
+__global__ void a1_to_c32_kernel(const float* __restrict__ a1, float* __restrict__ c32, int B) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B * C32_A1_PIX * 4) return;
+  const int u = i & 3, pix = (i >> 2) % C32_A1_PIX, img = i / (4 * C32_A1_PIX);
+  float v[8];
+#pragma unroll
+  for (int q = 0; q < 8; ++q) {
+    const int ci = u * 8 + q;
+    v[q] = 0.0f;
+    if (pix < 144) v[q] = ci < C1 ? a1[((size_t)img * C1 + ci) * 144 + pix] : (ci == C1 ? 1.0f : 0.0f);
+  }
+  float4* dst = reinterpret_cast<float4*>(c32 + ((size_t)img * C32_A1_PIX + pix) * 32 + ((u ^ (pix & 3)) * 8));
+  dst[0] = make_float4(v[0], v[1], v[2], v[3]);
+  dst[1] = make_float4(v[4], v[5], v[6], v[7]);
+}
+
+// pooled gradient -> swizzled c32 dZ [B][96][32]; one 32-byte unit per thread
+__global__ void conv2_dz_c32_kernel(const float* __restrict__ da2, const float* __restrict__ a2,
+                                    const uint8_t* __restrict__ pos2, const float* __restrict__ mask,
+                                    float* __restrict__ dz, int B) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B * C32_DZ_PIX * 4) return;
+  const int u = i & 3, q = (i >> 2) % C32_DZ_PIX, img = i / (4 * C32_DZ_PIX);
+  const int y = q / 12, x = q - y * 12;
+  float v[8];
+#pragma unroll
+  for (int c = 0; c < 8; ++c) {
+    const int co = u * 8 + c;
+    v[c] = 0.0f;
+    if (x < 8 && co < C2) {
+      const size_t gi = (size_t)img * A2_SZ + co * 16 + (y >> 1) * 4 + (x >> 1);
+      if (pos2[gi] == q && a2[gi] > 0.0f) v[c] = da2[gi] * (mask ? mask[(size_t)img * C2 + co] : 1.0f);
+    }
+  }
+  float4* dst = reinterpret_cast<float4*>(dz + ((size_t)img * C32_DZ_PIX + q) * 32 + ((u ^ (q & 3)) * 8));
+  dst[0] = make_float4(v[0], v[1], v[2], v[3]);
+  dst[1] = make_float4(v[4], v[5], v[6], v[7]);
+}
+
+__global__ void __launch_bounds__(CT_THREADS, 1)
+conv2_wgrad_tc_kernel(const float* __restrict__ a1_c32, const float* __restrict__ dz_c32,
+                      float* __restrict__ dw, float* __restrict__ db, int B) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* St = smem;                              // [stage]{a1 c32 20480 B, dZ c32 12288 B}
+  uint64_t* bars = reinterpret_cast<uint64_t*>(St + WG_STAGES * WG_STAGE_BYTES);
+  uint64_t* s_full = bars;
+  uint64_t* s_free = bars + WG_STAGES;
+  uint64_t* done = bars + 2 * WG_STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done + 1);
+  const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+
+  if (t == 0) {
+    for (int i = 0; i < WG_STAGES; ++i) { bar_init(s_full + i, 1); bar_init(s_free + i, 1); }
+    bar_init(done, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(s32(tmem_slot)) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp == 4 && lane == 0) {
+    int it = 0;
+    for (int img = blockIdx.x; img < B; img += gridDim.x, ++it) {
+      const int st = it % WG_STAGES;
+      if (it >= WG_STAGES) bar_wait(s_free + st, ((it / WG_STAGES) - 1) & 1);
+      uint8_t* dst = St + st * WG_STAGE_BYTES;
+      bar_expect(s_full + st, WG_STAGE_BYTES);
+      bulk_load(dst, a1_c32 + (size_t)img * (C32_A1_BYTES / 4), C32_A1_BYTES, s_full + st);
+      bulk_load(dst + C32_A1_BYTES, dz_c32 + (size_t)img * (C32_DZ_BYTES / 4), C32_DZ_BYTES, s_full + st);
+    }
+  } else if (warp == 5 && lane == 0) {
+    constexpr uint32_t idesc = idesc_tf32_mn(128, NPAD);
+    int it = 0;
+    for (int img = blockIdx.x; img < B; img += gridDim.x, ++it) {
+      const int st = it % WG_STAGES;
+      bar_wait(s_full + st, (it / WG_STAGES) & 1);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      const uint32_t a0 = s32(St + st * WG_STAGE_BYTES);
+      const uint32_t z0 = a0 + C32_A1_BYTES;
+#pragma unroll 1
+      for (int ks = 0; ks < 12; ++ks) {
+        const uint64_t bd = desc_mn_sw32atom(z0 + ks * 1024, 128, 512);      // N = 32: one group
+        const uint32_t acc = (it > 0 || ks > 0) ? 1u : 0u;
+#pragma unroll
+        for (int a = 0; a < 10; ++a) {
+          const int j0 = (a >> 1) * 12 + (a & 1) * 4;
+          const uint64_t ad = desc_mn_sw32atom(a0 + (ks * 8 + j0) * 128, 128, 512);   // LBO = one pixel
+          mma_tf32(tmem + a * NPAD, ad, bd, idesc, acc);
+        }
+      }
+      mma_commit(s_free + st);
+    }
+    mma_commit(done);
+  }
+  if (warp < 4) {
+    bar_wait(done, 0);
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    // lane l of warp w: GEMM row 32w + l = (shift w inside the window of 4, channel l)
+#pragma unroll 1
+    for (int a = 0; a < 10; ++a) {
+      uint32_t r[32];
+      tmem_ld32(tmem + a * NPAD + ((uint32_t)(warp * 32) << 16), r);
+      const int ky = a >> 1, kx = (a & 1) * 4 + warp, ci = lane;
+      if (kx < 5 && ci < C1) {
+#pragma unroll
+        for (int co = 0; co < C2; ++co)
+          atomicAdd(dw + (co * C1 + ci) * 25 + ky * 5 + kx, __uint_as_float(r[co]));
+      } else if (ci == C1 && a == 0 && warp == 0) {   // the ones channel at shift 0: bias gradient
+#pragma unroll
+        for (int co = 0; co < C2; ++co) atomicAdd(db + co, __uint_as_float(r[co]));
+      }
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem) : "memory");
+  }
+}
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
                                   const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
                                   const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -343,6 +676,88 @@ int b200_conv2_fwd_tc2(const float* a1_c4, const float* w, const float* b, float
   const int npairs = (B + 1) / 2;
   conv2_fwd_tc2_kernel<<<npairs < 148 ? npairs : 148, CT_THREADS, FWD_SMEM, (cudaStream_t)stream>>>(
       map, w, b, mask, mask_mode, p, seed, step, a2, (uint8_t*)pos2, B);
+  B200_LAUNCH_OK();
+  return 0;
+}
+
+// ---- backward entry points ---------------------------------------------------------------------
+int b200_conv2_frame_floats(int B) { return B * (DZ_IMG_BYTES / 4); }
+int b200_conv2_dgrad_operand_floats(void) { return WD_BYTES / 4; }
+
+// Pooled gradient da2 [B][20][4][4] (+ a2, pos2, Dropout2d mask or null) -> zero-padded dZ frame
+// [B][6][200][4] that both gradient kernels read. Ref: autograd of src/model.py:24.
+int b200_conv2_dz_frame(const float* da2, const float* a2, const void* pos2, const float* mask,
+                        float* frame, int B, void* stream) {
+  if (B <= 0) return 0;
+  const int n = B * DZ_CHUNKS * FRAME;
+  conv2_dz_frame_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(da2, a2, (const uint8_t*)pos2,
+                                                                           mask, frame, B);
+  B200_LAUNCH_OK();
+  return 0;
+}
+
+// conv2.weight -> flipped data-gradient operand (b200_conv2_dgrad_operand_floats() floats).
+int b200_conv2_w_to_dgrad_operand(const float* w, float* wd, void* stream) {
+  const int n = 25 * DZ_CHUNKS * CIPAD;
+  conv2_w_to_dgrad_operand_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(w, wd);
+  B200_LAUNCH_OK();
+  return 0;
+}
+
+// da1 [B][10][12][12] = conv2 data gradient of the dZ frame (tcgen05, TF32 operands).
+int b200_conv2_dgrad_tc(const float* frame, const float* wd, float* da1, int B, void* stream) {
+  if (B <= 0) return 0;
+  B200_REQUIRE((((uintptr_t)frame | (uintptr_t)wd) & 15) == 0, "b200_conv2_dgrad_tc: operands must be 16-byte aligned");
+  static bool attr_done[64] = {false};
+  int dev = 0;
+  B200_CUDA_OK(cudaGetDevice(&dev));
+  if (!attr_done[dev & 63]) {
+    B200_CUDA_OK(cudaFuncSetAttribute(conv2_dgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DG_SMEM));
+    attr_done[dev & 63] = true;
+  }
+  conv2_dgrad_tc_kernel<<<B < 148 ? B : 148, CT_THREADS, DG_SMEM, (cudaStream_t)stream>>>(frame, wd, da1, B);
+  B200_LAUNCH_OK();
+  return 0;
+}
+
+int b200_conv2_c32_a1_floats(int B) { return B * (C32_A1_BYTES / 4); }
+int b200_conv2_c32_dz_floats(int B) { return B * (C32_DZ_BYTES / 4); }
+
+// a1 [B][10][12][12] -> the weight gradient's A operand (b200_conv2_c32_a1_floats(B) floats).
+int b200_a1_to_c32(const float* a1, float* c32, int B, void* stream) {
+  if (B <= 0) return 0;
+  const int n = B * C32_A1_PIX * 4;
+  a1_to_c32_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(a1, c32, B);
+  B200_LAUNCH_OK();
+  return 0;
+}
+
+// pooled gradient -> the weight gradient's B operand (b200_conv2_c32_dz_floats(B) floats).
+int b200_conv2_dz_c32(const float* da2, const float* a2, const void* pos2, const float* mask,
+                      float* dz, int B, void* stream) {
+  if (B <= 0) return 0;
+  const int n = B * C32_DZ_PIX * 4;
+  conv2_dz_c32_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(da2, a2, (const uint8_t*)pos2,
+                                                                         mask, dz, B);
+  B200_LAUNCH_OK();
+  return 0;
+}
+
+// dw [20][10][5][5] and db [20] (both overwritten) from the two c32 operands (tcgen05, TF32
+// operands; the CTAs' partial sums meet in fp32 atomics).
+int b200_conv2_wgrad_tc(const float* a1_c4, const float* frame, float* dw, float* db, int B, void* stream) {
+  B200_REQUIRE(B > 0, "b200_conv2_wgrad_tc: empty batch");
+  B200_REQUIRE((((uintptr_t)frame | (uintptr_t)a1_c4) & 511) == 0, "b200_conv2_wgrad_tc: operands must be 512-byte aligned");
+  static bool attr_done[64] = {false};
+  int dev = 0;
+  B200_CUDA_OK(cudaGetDevice(&dev));
+  if (!attr_done[dev & 63]) {
+    B200_CUDA_OK(cudaFuncSetAttribute(conv2_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, WG_SMEM));
+    attr_done[dev & 63] = true;
+  }
+  B200_CUDA_OK(cudaMemsetAsync(dw, 0, W2_SZ * sizeof(float), (cudaStream_t)stream));
+  B200_CUDA_OK(cudaMemsetAsync(db, 0, B2_SZ * sizeof(float), (cudaStream_t)stream));
+  conv2_wgrad_tc_kernel<<<B < 148 ? B : 148, CT_THREADS, WG_SMEM, (cudaStream_t)stream>>>(a1_c4, frame, dw, db, B);
   B200_LAUNCH_OK();
   return 0;
 }

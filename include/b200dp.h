@@ -214,6 +214,26 @@ int b200_conv2_operand_floats(void);
 int b200_conv2_fwd_tc2(const float* a1_c4, const float* w_operand, const float* b, float* mask, int mask_mode,
                        float p, unsigned long long seed, unsigned long long step, float* a2,
                        void* pos2, int B, void* stream);
+
+/* conv2 backward on tcgen05 (csrc/conv2_tc.cu). b200_conv2_dz_frame scatters the pooled gradient
+ * into a zero-padded frame [B][6][200][4] (b200_conv2_frame_floats(B) floats) that
+ * the data-gradient kernel reads through UMMA descriptors only, as an implicit GEMM over
+ * flipped taps (weights from b200_conv2_w_to_dgrad_operand). Ref: autograd of
+ * src/model.py:24 run by src/train_dist.py:83 */
+int b200_conv2_frame_floats(int B);
+int b200_conv2_dgrad_operand_floats(void);
+int b200_conv2_dz_frame(const float* da2, const float* a2, const void* pos2, const float* mask,
+                        float* frame, int B, void* stream);
+int b200_conv2_w_to_dgrad_operand(const float* w, float* wd, void* stream);
+int b200_conv2_dgrad_tc(const float* frame, const float* wd, float* da1, int B, void* stream);
+/* weight + bias gradient: both operands MN-major in the swizzled [pixel][32 channels] layout
+ * written by b200_a1_to_c32 / b200_conv2_dz_c32 (512-byte aligned buffers) */
+int b200_conv2_c32_a1_floats(int B);
+int b200_conv2_c32_dz_floats(int B);
+int b200_a1_to_c32(const float* a1, float* c32, int B, void* stream);
+int b200_conv2_dz_c32(const float* da2, const float* a2, const void* pos2, const float* mask,
+                      float* dz, int B, void* stream);
+int b200_conv2_wgrad_tc(const float* a1_c32, const float* dz_c32, float* dw, float* db, int B, void* stream);
 /* MLP helpers: fused softmax + NLL + gradient, bias gradient, master-weight SGD. */
 int b200_softmax_nll_bf16(const float* logits, int ld, int ncls, const long long* labels,
                           float* loss, void* dlogits, int ld_d, int B, void* stream);

@@ -282,6 +282,52 @@ def test_conv2_tc_implicit_gemm_matches_oracle(cuda_device, B):
     torch.testing.assert_close(got, simt, rtol=5e-3, atol=5e-3)
 
 
+@pytest.mark.parametrize("B", [1, 3, 64, 200, 512, 1000])
+def test_conv2_tc_backward_matches_oracle(cuda_device, B):
+    """conv2 data, weight and bias gradients on tcgen05 (csrc/conv2_tc.cu: implicit GEMM over
+    a zero-padded dZ frame; MN-major pixel-reduction GEMM) vs fp64 autograd of the same layer
+    with the same arg-max positions, and vs the SIMT kernel (autograd of src/model.py:24)."""
+    torch.manual_seed(2)
+    net = Net()
+    g = torch.Generator().manual_seed(100 + B)
+    a1 = torch.relu(torch.randn(B, 10, 12, 12, generator=g))
+    m2 = oracle.make_masks(B, g)[0]
+    da2 = torch.randn(B, 20, 4, 4, generator=g)
+    w, b = net.conv2.weight.detach(), net.conv2.bias.detach()
+    dev = cuda_device
+    # forward state from the fp32-exact kernel: a2 and the arg-max position of every window
+    N = net_ops.N
+    a2 = torch.empty(B, 20, 4, 4, device=dev)
+    pos2 = torch.empty(B, 20, 4, 4, dtype=torch.uint8, device=dev)
+    a1d, wd_, bd, md = a1.to(dev), w.to(dev), b.to(dev), m2.to(dev)
+    N.call("b200_conv2_fwd", N.ptr(a1d), N.ptr(wd_), N.ptr(bd), N.ptr(md), 2, 0.5, 0, 0,
+           N.ptr(a2), N.ptr(pos2), B, N.stream())
+    da1, dw, db = net_ops.conv2_backward_tc(a1d, wd_, a2, pos2, md, da2.to(dev))
+    # fp64 reference: dense dZ from the same positions, then autograd of the convolution
+    p = pos2.cpu().long()
+    live = (a2.cpu() > 0).double() * m2.double().view(B, 20, 1, 1) * da2.double()
+    dz = torch.zeros(B, 20, 96, dtype=torch.float64)
+    dz.scatter_(2, p.view(B, 20, 16), live.view(B, 20, 16))
+    dz = dz.view(B, 20, 8, 12)[..., :8]
+    a1r, wr = a1.double().requires_grad_(True), w.double().requires_grad_(True)
+    torch.nn.functional.conv2d(a1r, wr).backward(dz)
+
+    def close(got, want, what):
+        scale = float(want.abs().max()) + 1e-12
+        err = float((got.cpu().double() - want).abs().max()) / scale
+        assert err < 4e-3, f"{what}: max error {err:.2e} of the largest entry"      # TF32 operands
+    close(da1, a1r.grad, "da1")
+    close(dw, wr.grad, "dw")
+    close(db, dz.sum(dim=(0, 2, 3)), "db")
+    # and the SIMT backward from the same saved state
+    ws = net_ops.workspace(dev)
+    dw_s, db_s, da1_s = torch.empty_like(wd_), torch.empty(20, device=dev), torch.empty_like(a1d)
+    N.call("b200_conv2_bwd", N.ptr(a1d), N.ptr(wd_), N.ptr(da2.to(dev)), N.ptr(a2), N.ptr(pos2), N.ptr(md),
+           N.ptr(dw_s), N.ptr(db_s), N.ptr(da1_s), N.ptr(ws.scratch), N.ptr(ws.counter), B, N.stream())
+    close(da1, da1_s.cpu().double(), "da1 vs SIMT")
+    close(dw, dw_s.cpu().double(), "dw vs SIMT")
+
+
 @pytest.mark.parametrize("B", [1, 2, 7, 64, 1000])
 def test_conv2_tcgen05_matches_oracle(cuda_device, B):
     """conv2 + dropout2d + pool + relu on tcgen05 (TF32) vs the fp32 oracle of the layer."""
