@@ -47,6 +47,10 @@ __device__ __forceinline__ uint64_t desc_k_noswz(uint32_t addr, uint32_t lbo, ui
   return d;                               // layout type 0: no swizzle
 }
 
+// start address + bytes: the field holds address >> 4 in the low 14 bits and a valid shared-memory
+// address never carries out of it
+__device__ __forceinline__ uint64_t desc_advance(uint64_t d, uint32_t bytes) { return d + (uint64_t)(bytes >> 4); }
+
 __device__ __forceinline__ void mma_tf32(uint32_t tmem, uint64_t ad, uint64_t bd, uint32_t idesc,
                                          uint32_t accumulate) {
   asm volatile(
@@ -198,18 +202,15 @@ conv2_fwd_tc2_kernel(const __grid_constant__ CUtensorMap map_a1, const float* __
       if (it >= 2) bar_wait(acc_free + buf, ((it >> 1) - 1) & 1);
       bar_wait(a_full + st, (it / STAGES) & 1);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-      const uint32_t a0 = s32(As + st * A_BYTES);
-      uint32_t acc = 0;
-#pragma unroll 1
+      const uint64_t ad0 = desc_k_noswz(s32(As + st * A_BYTES), A_CHUNK_BYTES, 12 * 16);
+      const uint64_t bd0 = desc_k_noswz(b0, NPAD * 16, 128);
+#pragma unroll
       for (int tap = 0; tap < 25; ++tap) {
         const int ky = tap / 5, kx = tap - ky * 5;
 #pragma unroll
-        for (int kc = 0; kc < 2; ++kc) {
-          const uint64_t ad = desc_k_noswz(a0 + (2 * kc) * A_CHUNK_BYTES + (ky * 24 + kx) * 16, A_CHUNK_BYTES, 12 * 16);
-          const uint64_t bd = desc_k_noswz(b0 + tap * B_TAP_BYTES + (2 * kc) * (NPAD * 16), NPAD * 16, 128);
-          mma_tf32(tmem + buf * NPAD, ad, bd, idesc, acc);
-          acc = 1;
-        }
+        for (int kc = 0; kc < 2; ++kc)
+          mma_tf32(tmem + buf * NPAD, desc_advance(ad0, (2 * kc) * A_CHUNK_BYTES + (ky * 24 + kx) * 16),
+                   desc_advance(bd0, tap * B_TAP_BYTES + (2 * kc) * (NPAD * 16)), idesc, (tap | kc) ? 1u : 0u);
       }
       mma_commit(a_free + st);
       mma_commit(acc_full + buf);
@@ -338,7 +339,8 @@ __device__ __forceinline__ void bar_expect(uint64_t* bar, uint32_t bytes) {
 // ---- data gradient -----------------------------------------------------------------------------
 // Persistent, one image per pipeline stage. warp 4 lane 0: bulk copies (the flipped weights once,
 // then one 19,200-byte dZ frame per image); warp 5 lane 0: 2 tiles x 25 taps x 3 K-steps of
-// tcgen05.mma.kind::tf32 (M=128, N=16, K=8); warps 0-3: TMEM -> da1 [B][10][12][12].
+// tcgen05.mma.kind::tf32 (M=128, N=16, K=8), warp 6 lane 0 the same for the second tile;
+// warps 0-3: TMEM -> da1 [B][10][12][12].
 __global__ void __launch_bounds__(CT_THREADS, 1)
 conv2_dgrad_tc_kernel(const float* __restrict__ frame, const float* __restrict__ wd,
                       float* __restrict__ da1, int B) {
@@ -356,8 +358,8 @@ conv2_dgrad_tc_kernel(const float* __restrict__ frame, const float* __restrict__
   const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
 
   if (t == 0) {
-    for (int i = 0; i < DG_STAGES; ++i) { bar_init(a_full + i, 1); bar_init(a_free + i, 1); }
-    for (int i = 0; i < 2; ++i) { bar_init(acc_full + i, 1); bar_init(acc_free + i, 4); }
+    for (int i = 0; i < DG_STAGES; ++i) { bar_init(a_full + i, 1); bar_init(a_free + i, 2); }
+    for (int i = 0; i < 2; ++i) { bar_init(acc_full + i, 2); bar_init(acc_free + i, 4); }
     bar_init(w_full, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -381,9 +383,12 @@ conv2_dgrad_tc_kernel(const float* __restrict__ frame, const float* __restrict__
       bar_expect(a_full + st, DZ_IMG_BYTES);
       bulk_load(As + st * DZ_IMG_BYTES, frame + (size_t)img * (DZ_IMG_BYTES / 4), DZ_IMG_BYTES, a_full + st);
     }
-  } else if (warp == 5 && lane == 0) {
+  } else if ((warp == 5 || warp == 6) && lane == 0) {
+    // two issuing threads, one per M tile: the issue path of one thread, not the tensor pipe,
+    // bounds a stream of small MMAs; each commits its own MMAs to the (count 2) barriers
     constexpr uint32_t idesc = idesc_tf32(128, CIPAD);
     const uint32_t b0 = s32(Bs);
+    const int tile = warp - 5;
     bar_wait(w_full, 0);
     int it = 0;
     for (int img = blockIdx.x; img < B; img += gridDim.x, ++it) {
@@ -391,21 +396,17 @@ conv2_dgrad_tc_kernel(const float* __restrict__ frame, const float* __restrict__
       if (it >= 2) bar_wait(acc_free + buf, ((it >> 1) - 1) & 1);
       bar_wait(a_full + st, (it / DG_STAGES) & 1);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-      const uint32_t a0 = s32(As + st * DZ_IMG_BYTES);
-#pragma unroll 1
-      for (int tile = 0; tile < 2; ++tile) {
-        uint32_t acc = 0;
-#pragma unroll 1
+      const uint64_t bd0 = desc_k_noswz(b0, CIPAD * 16, 128);
+      {
+        const uint64_t ad0 = desc_k_noswz(s32(As + st * DZ_IMG_BYTES) + tile * (128 * 16), DZ_PLANE_BYTES, 128);
+        const uint32_t d = tmem + (buf * 2 + tile) * CIPAD;
+#pragma unroll
         for (int tp = 0; tp < 25; ++tp) {
           const int ky = tp / 5, kx = tp - ky * 5;
-          const uint32_t arow = a0 + (uint32_t)(tile * 128 + ky * 12 + kx) * 16;
 #pragma unroll
-          for (int kc = 0; kc < 3; ++kc) {
-            const uint64_t ad = desc_k_noswz(arow + (2 * kc) * DZ_PLANE_BYTES, DZ_PLANE_BYTES, 128);
-            const uint64_t bd = desc_k_noswz(b0 + tp * WD_TAP_BYTES + (2 * kc) * (CIPAD * 16), CIPAD * 16, 128);
-            mma_tf32(tmem + (buf * 2 + tile) * CIPAD, ad, bd, idesc, acc);
-            acc = 1;
-          }
+          for (int kc = 0; kc < 3; ++kc)
+            mma_tf32(d, desc_advance(ad0, (ky * 12 + kx) * 16 + (2 * kc) * DZ_PLANE_BYTES),
+                     desc_advance(bd0, tp * WD_TAP_BYTES + (2 * kc) * (CIPAD * 16)), idesc, (tp | kc) ? 1u : 0u);
         }
       }
       mma_commit(a_free + st);
@@ -525,8 +526,8 @@ conv2_wgrad_tc_kernel(const float* __restrict__ a1_c32, const float* __restrict_
   const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
 
   if (t == 0) {
-    for (int i = 0; i < WG_STAGES; ++i) { bar_init(s_full + i, 1); bar_init(s_free + i, 1); }
-    bar_init(done, 1);
+    for (int i = 0; i < WG_STAGES; ++i) { bar_init(s_full + i, 1); bar_init(s_free + i, 2); }
+    bar_init(done, 2);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -548,24 +549,27 @@ conv2_wgrad_tc_kernel(const float* __restrict__ a1_c32, const float* __restrict_
       bulk_load(dst, a1_c32 + (size_t)img * (C32_A1_BYTES / 4), C32_A1_BYTES, s_full + st);
       bulk_load(dst + C32_A1_BYTES, dz_c32 + (size_t)img * (C32_DZ_BYTES / 4), C32_DZ_BYTES, s_full + st);
     }
-  } else if (warp == 5 && lane == 0) {
+  } else if ((warp == 5 || warp == 6) && lane == 0) {
+    // two issuing threads with five accumulators each (see the data-gradient kernel)
     constexpr uint32_t idesc = idesc_tf32_mn(128, NPAD);
+    const int abase = (warp - 5) * 5;
     int it = 0;
     for (int img = blockIdx.x; img < B; img += gridDim.x, ++it) {
       const int st = it % WG_STAGES;
       bar_wait(s_full + st, (it / WG_STAGES) & 1);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       const uint32_t a0 = s32(St + st * WG_STAGE_BYTES);
-      const uint32_t z0 = a0 + C32_A1_BYTES;
-#pragma unroll 1
+      const uint64_t ad0 = desc_mn_sw32atom(a0, 128, 512);                    // LBO = one pixel
+      const uint64_t bd0 = desc_mn_sw32atom(a0 + C32_A1_BYTES, 128, 512);     // N = 32: one group
+#pragma unroll 2
       for (int ks = 0; ks < 12; ++ks) {
-        const uint64_t bd = desc_mn_sw32atom(z0 + ks * 1024, 128, 512);      // N = 32: one group
         const uint32_t acc = (it > 0 || ks > 0) ? 1u : 0u;
+        const uint64_t bd = desc_advance(bd0, ks * 1024);
+        const uint64_t adk = desc_advance(ad0, ks * 1024);
 #pragma unroll
-        for (int a = 0; a < 10; ++a) {
-          const int j0 = (a >> 1) * 12 + (a & 1) * 4;
-          const uint64_t ad = desc_mn_sw32atom(a0 + (ks * 8 + j0) * 128, 128, 512);   // LBO = one pixel
-          mma_tf32(tmem + a * NPAD, ad, bd, idesc, acc);
+        for (int i = 0; i < 5; ++i) {
+          const int a = abase + i;
+          mma_tf32(tmem + a * NPAD, desc_advance(adk, ((a >> 1) * 12 + (a & 1) * 4) * 128), bd, idesc, acc);
         }
       }
       mma_commit(s_free + st);

@@ -365,6 +365,46 @@ def test_net_with_tcgen05_conv2_trains(cuda_device):
         assert err < 2e-2
 
 
+@pytest.mark.parametrize("B", [64, 512])
+def test_net_with_tc_conv2_follows_oracle_loss_curve(cuda_device, B):
+    """The layered path with conv2 forward, data gradient and weight gradient all on tcgen05
+    (Net(conv2_impl="tc"), TF32 operands): gradients of the first step against the fp64 oracle,
+    then 100 SGD-momentum steps on a learnable 10-template set whose loss curve stays on the
+    oracle's (the loop of src/train.py:66-76)."""
+    torch.manual_seed(1)
+    net = Net(conv2_impl="tc").to(cuda_device).train()
+    ref = _oracle_params(net)
+    bufs = [torch.zeros_like(p) for p in ref]
+    opt = torch.optim.SGD(net.parameters(), lr=0.02, momentum=0.5)
+    g = torch.Generator().manual_seed(3)
+    templates = torch.randn(10, 784, generator=g)
+    ours, theirs = [], []
+    for it in range(100):
+        y = torch.randint(0, 10, (B,), generator=g)
+        x = (templates[y] + 0.5 * torch.randn(B, 784, generator=g)).view(B, 1, 28, 28)
+        m2, m3 = oracle.make_masks(B, torch.Generator().manual_seed(100 + it))
+        opt.zero_grad(set_to_none=True)
+        loss = net_ops.nll_loss(net(x.to(cuda_device), masks=(m2.to(cuda_device), m3.to(cuda_device))),
+                                y.to(cuda_device))
+        loss.backward()
+        for p in ref:
+            p.grad = None
+        lo = oracle.net_loss(ref, x.double(), y, m2.double(), m3.double())
+        lo.backward()
+        if it == 0:
+            for name, p_, q in zip(Net.PARAM_ORDER, net.param_list(), ref):
+                err = (p_.grad.cpu() - q.grad.float()).norm() / (q.grad.float().norm() + 1e-12)
+                # TF32 products move a few pooling arg-max positions, which reroutes those gradients
+                assert err < 3e-2, f"first-step gradient of {name}: relative error {float(err):.2e}"
+        opt.step()
+        oracle.sgd_momentum_step(ref, [q.grad for q in ref], bufs, 0.02, 0.5)
+        ours.append(float(loss.detach()))
+        theirs.append(float(lo.detach()))
+    worst = max(abs(a - b) / max(abs(b), 0.05) for a, b in zip(ours, theirs))
+    assert worst < 5e-2, f"loss curves part by {worst:.2e}: {ours[-3:]} vs {theirs[-3:]}"
+    assert sum(ours[-10:]) / 10 < 0.5 * sum(ours[:10]) / 10
+
+
 def test_resident_epoch_multistep_graph_equals_eager(cuda_device):
     """Device-side index stepping + 16-step graphs (PDL across steps) == one eager step at a time."""
     from csed_514_project_distributed_training_using_pytorch_b200.ops.fused import X_U8_GATHER
