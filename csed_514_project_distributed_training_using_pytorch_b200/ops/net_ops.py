@@ -87,7 +87,11 @@ class Conv2DropPoolRelu(torch.autograd.Function):
         # "tc": TF32 implicit GEMM without im2col, TMA-fed (csrc/conv2_tc.cu);
         # "tcgen05": the first tensor-core version with an in-smem im2col (csrc/conv_tcgen05.cu);
         # "simt": fp32-exact CUDA-core kernel (csrc/net_kernels.cu)
-        if impl == "tc":
+        # "auto": the measured choice for the layered path (profiles/r2/conv2_bwd_bench.json,
+        #         conv2_tc_bench.json): tensor-core backward always (5-9x the SIMT kernel),
+        #         tensor-core forward from batch 2048 up
+        fwd_tc = impl == "tc" or (impl == "auto" and B >= 2048)
+        if fwd_tc:
             c4 = torch.empty(B, 4, 12, 12, 4, dtype=torch.float32, device=a1.device)
             N.call("b200_a1_to_c4", N.ptr(a1), N.ptr(c4), B, N.stream())
             wop = torch.empty(N.lib().b200_conv2_operand_floats(), dtype=torch.float32, device=a1.device)
@@ -98,7 +102,7 @@ class Conv2DropPoolRelu(torch.autograd.Function):
             N.call("b200_conv2_fwd_tc" if impl == "tcgen05" else "b200_conv2_fwd", N.ptr(a1), N.ptr(w),
                    N.ptr(b), N.ptr(mask), mask_mode, float(p),
                    int(seed), int(step), N.ptr(a2), N.ptr(pos2), B, N.stream())
-        ctx.tc = impl == "tc"
+        ctx.tc = impl in ("tc", "auto")
         ctx.save_for_backward(a1, w, a2, pos2, mask if mask_mode else None)
         return a2
 

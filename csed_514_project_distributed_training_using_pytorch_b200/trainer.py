@@ -62,7 +62,7 @@ class Trainer:
         else:
             self.device = torch.device("cpu")
         torch.manual_seed(cfg.random_seed)               # src/train.py:21, src/train_dist.py:137
-        self.model = (model or Net()).to(self.device)
+        self.model = (model or Net(conv2_impl=cfg.conv2_impl)).to(self.device)
         self.log = logger or MetricsLogger(rank=self.rank)
         self.engine: Optional[FusedNetEngine] = None
         self.ddp = None

@@ -39,6 +39,7 @@ class TrainConfig:
     device: str = "cuda"            # "cpu" runs the PyTorch oracle path (BASELINE config 1)
     fused: bool = True              # fused 2-kernel step; False = layered autograd path
     cuda_graph: bool = True
+    conv2_impl: str = "simt"        # layered path only: "simt" fp32 | "tc" TF32 on tcgen05 | "auto"
     dropout: bool = True
     input_dtype: str = "u8"         # how the dataset is stored: "u8" (MNIST native) or "f32"
     feed: str = "resident"          # "resident": dataset in HBM, the kernel gathers its batch;

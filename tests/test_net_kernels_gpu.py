@@ -405,6 +405,29 @@ def test_net_with_tc_conv2_follows_oracle_loss_curve(cuda_device, B):
     assert sum(ours[-10:]) / 10 < 0.5 * sum(ours[:10]) / 10
 
 
+def test_conv2_auto_uses_tensor_core_backward(cuda_device):
+    """conv2_impl="auto": fp32 forward below batch 2048 (bit-equal to "simt"), tcgen05 backward."""
+    torch.manual_seed(3)
+    net = Net()
+    B = 96
+    g = torch.Generator().manual_seed(5)
+    a1 = torch.relu(torch.randn(B, 10, 12, 12, generator=g)).to(cuda_device)
+    m2 = oracle.make_masks(B, g)[0].to(cuda_device)
+    da2 = torch.randn(B, 20, 4, 4, generator=g).to(cuda_device)
+    grads = {}
+    for impl in ("simt", "auto"):
+        a = a1.clone().requires_grad_(True)
+        w = net.conv2.weight.detach().to(cuda_device).requires_grad_(True)
+        b = net.conv2.bias.detach().to(cuda_device).requires_grad_(True)
+        out = net_ops.conv2_drop_pool_relu(a, w, b, m2, 2, impl=impl)
+        out.backward(da2)
+        grads[impl] = (out.detach(), a.grad, w.grad, b.grad)
+    assert torch.equal(grads["simt"][0], grads["auto"][0])
+    for got, want in zip(grads["auto"][1:], grads["simt"][1:]):
+        assert float((got - want).abs().max()) < 4e-3 * float(want.abs().max())
+        assert not torch.equal(got, want)          # TF32 products: the tensor-core kernels ran
+
+
 def test_resident_epoch_multistep_graph_equals_eager(cuda_device):
     """Device-side index stepping + 16-step graphs (PDL across steps) == one eager step at a time."""
     from csed_514_project_distributed_training_using_pytorch_b200.ops.fused import X_U8_GATHER
