@@ -555,15 +555,19 @@ template <typename ColFn>
 __device__ __forceinline__ bool exchange_update(const PersistArgs& a, const float4* gs, int nitems,
                                                 ColFn col_of, unsigned seq, bool write_grad,
                                                 uint2* box = nullptr, int box_col0 = 0,
-                                                unsigned tag = 0u) {
-  const int t = threadIdx.x;
+                                                unsigned tag = 0u, int phase = 0, int t = -1,
+                                                int nthreads = NT) {
+  // phase 0: push to the peers, then gather + update; 1: push only; 2: gather + update only
+  // (the caller pushed earlier). t / nthreads: the threads that take part (default: the CTA).
+  if (t < 0) t = threadIdx.x;
   const bool multi = a.multi && a.comm.world > 1;
-  if (multi)
-    for (int i = t; i < nitems; i += NT) ll_push(a, col_of(i), gs[i], seq);
+  if (multi && phase != 2)
+    for (int i = t; i < nitems; i += nthreads) ll_push(a, col_of(i), gs[i], seq);
+  if (phase == 1) return true;
   const float lr = a.hp[0], mu = a.hp[1];
   const float inv = multi ? 1.0f / (float)a.comm.world : 1.0f;
   bool ok = true;
-  for (int i = t; i < nitems; i += NT) {
+  for (int i = t; i < nitems; i += nthreads) {
     const int col = col_of(i);
     float4 pv = make_float4(0.f, 0.f, 0.f, 0.f), bv = pv;
     if (a.update || box) pv = ldcg4(a.params + 4 * col);   // operands of the update do not
@@ -721,6 +725,9 @@ __device__ __forceinline__ void worker_loop(const PersistArgs& a, float* smem) {
   constexpr int FETCH_T = 288;   // lane 0 of warp 9
   constexpr unsigned long long W2_COPY_DELAY_NS = 900ull;
   unsigned long long bubble_end_ns = 0ull;
+  bool pending = false;            // a pushed conv2 slice waits for its gather + update
+  int pend_c0 = 0, pend_nc = 0;
+  unsigned pend_seq = 0u, pend_tag = 0u;
   constexpr int SIGNAL_T = 300;  // a thread of warp 9 that the backward's wide phases leave idle
   for (int k = 0; k < nitems; ++k) {
     int ls, img;
@@ -761,7 +768,24 @@ __device__ __forceinline__ void worker_loop(const PersistArgs& a, float* smem) {
       }
     };
     if (t == FETCH_T && issued <= k) { issue_image(k, true); issued = k + 1; }
-    if (t == FETCH_T && first_of_step && ls > 0) {
+    const bool finish_conv2 = first_of_step && pending;
+    if (finish_conv2) {
+      // Several GPUs: the conv2 slice was only PUSHED to the peers in the bubble. While the
+      // other warps wait for conv1's weights (whose exchange is the longer trip), warp 9 waits
+      // for the peers' words, sums them, applies SGD-momentum and publishes the slice, then
+      // pulls the whole mailbox in: the conv2 exchange overlaps conv1's instead of preceding it.
+      if (t >= FETCH_T) {
+        const int c0 = pend_c0;
+        const bool ok = exchange_update(a, reinterpret_cast<const float4*>(w.Ts), pend_nc,
+                                        [=](int i) { return OFF_W2 / 4 + c0 + i; }, pend_seq, false,
+                                        a.w2box, OFF_W2 / 4, pend_tag, 2, t - FETCH_T, NT - FETCH_T);
+        if (!ok) atomicExch(ctl + C_ABORT * CTL_STRIDE, 1u);
+        __syncwarp();
+        if (t == FETCH_T) bubble_end_ns = globaltimer_ns();   // published; the copy follows below
+      }
+      pending = false;
+    }
+    if (t == FETCH_T && first_of_step && ls > 0 && !finish_conv2) {
       // Every worker published its conv2 slice at the end of its bubble, all within a fraction
       // of a microsecond of each other. Give the last ones time to land, then pull the whole
       // mailbox in with one bulk copy that completes under conv1's forward; a word copied too
@@ -843,6 +867,10 @@ __device__ __forceinline__ void worker_loop(const PersistArgs& a, float* smem) {
     if (w.flags[0] != 0) break;     // uniform: one thread sampled the abort word
     PSTAMP(ls, 1);
     bool fc_issued = !first_of_step;
+    if (t == FETCH_T && finish_conv2) {          // under conv1's forward, which warp 9 sits out
+      while (globaltimer_ns() - bubble_end_ns < W2_COPY_DELAY_NS) { }
+      fetch_conv2();
+    }
     if (t == FETCH_T && first_of_step) {
       if (ls == 0) fetch_conv2();                // later steps: issued during the wait for conv1's weights
       fc_issued = fetch_fc(false);               // fc only if it is already published
@@ -987,10 +1015,16 @@ __device__ __forceinline__ void worker_loop(const PersistArgs& a, float* smem) {
       float4* gs = reinterpret_cast<float4*>(w.Ts);
       float4* red = gs + ((per + 3) & ~3);
       reduce_rows_slice<4>(a, ls, a.part2, a.rows, P2_ROW, c0, nc, gs, red);
+      // with peers and another step to come, only push now and finish under the next conv1
+      const bool defer = a.multi && a.comm.world > 1 && k + 1 < nitems;
       const bool ok = exchange_update(a, gs, nc, [=](int i) { return OFF_W2 / 4 + c0 + i; },
                                       seq0 + (unsigned)ls + 1u, a.grad_out != nullptr && ls == a.nsteps - 1,
-                                      a.w2box, OFF_W2 / 4, a.tag_base | (unsigned)(ls + 1));
+                                      a.w2box, OFF_W2 / 4, a.tag_base | (unsigned)(ls + 1), defer ? 1 : 0);
       if (!ok) atomicExch(ctl + C_ABORT * CTL_STRIDE, 1u);
+      if (defer) {
+        pending = true; pend_c0 = c0; pend_nc = nc;
+        pend_seq = seq0 + (unsigned)ls + 1u; pend_tag = a.tag_base | (unsigned)(ls + 1);
+      }
       __syncthreads();               // the T buffer is the next step's mailbox landing zone
       if (t == FETCH_T) bubble_end_ns = globaltimer_ns();
       PSTAMP(ls, 12);

@@ -71,15 +71,12 @@ def main():
     eng.check_errors()
     if comm is not None:
         comm.host_barrier()
-        if rank != 0:
-            P.destroy_process_group()
-            return
     d = dbg.cpu()
     clk, gt = d[..., 0].double(), d[..., 1].double()
     W = plan["workers"]
     lo, hi = 4, min(S, d.shape[1]) - 1          # steady-state steps
     lines = [f"# Persistent step kernel: phase timeline, batch {B}, {S} steps per launch, "
-             f"{world} GPU(s) (rank 0's CTAs)", "",
+             f"{world} GPU(s) (rank {rank}'s CTAs)", "",
              f"Plan: {plan}", ""]
     # SM clock from the two time bases (cycles per ns over the whole launch, CTA 0)
     cyc = clk[0, hi, 0] - clk[0, lo, 0]
@@ -143,10 +140,26 @@ def main():
     starts = [float((gt[:W, i, 0].median() - t_first) / 1e3) for i in range(min(10, S))]
     lines += ["", "## Start of the first steps after the first CTA's first stamp (us): "
               + ", ".join(f"{v:.1f}" for v in starts)]
+    # per-step trace of the link between two steps (global timer, us after the median worker
+    # started the step): when the workers' conv1 rows were complete, when the conv1 service CTA
+    # had them summed / exchanged / published, when the workers had the new conv1 weights
+    lines += ["", "## Per-step trace of the conv1 link (us after the median worker started step s)", "",
+              "| step | period | median worker: conv1 wgrad done | slowest worker: conv1 wgrad done | "
+              "median worker: bubble done | service: rows summed | service: exchanged + SGD | "
+              "service: published | median worker: has conv1 weights of step s (next step) |",
+              "|---|---|---|---|---|---|---|---|---|"]
+    for st in range(lo, min(hi, lo + 12)):
+        o = gt[:W, st, 0].median()
+        f = lambda v: f"{float(v - o) / 1e3:.2f}"
+        nxt = gt[:W, st + 1, 1].median() if st + 1 < d.shape[1] else o
+        lines.append(f"| {st} | {float(gt[:W, st + 1, 0].median() - o) / 1e3:.2f} | {f(gt[:W, st, 11].median())} | "
+                     f"{f(gt[:W, st, 11].max())} | {f(gt[:W, st, 12].median())} | {f(gt[W, st, 1])} | "
+                     f"{f(gt[W, st, 3])} | {f(gt[W, st, 4])} | {f(nxt)} |")
     text = "\n".join(lines) + "\n"
-    print(text)
-    if a.out:
-        Path(a.out).write_text(text)
+    if rank == 0:
+        print(text)
+    if a.out:      # every rank reports its own CTAs
+        Path(a.out if rank == 0 else f"{a.out}.rank{rank}").write_text(text)
     if comm is not None:
         P.destroy_process_group()
 
