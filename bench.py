@@ -246,9 +246,14 @@ def run_ours(a):
         t0 = time.perf_counter()
         e0.record()
         losses = host_steps(K)
+        t_enq = time.perf_counter()
         e1.record()
         torch.cuda.synchronize()          # this rank's last loss is in host memory
         wall_ms = (time.perf_counter() - t0) * 1e3   # before the host barrier: gloo is not part of a step
+        if os.environ.get("B200DP_BENCH_DEBUG"):
+            import sys
+            print(f"[bench debug] e2e: enqueue returned after {(t_enq - t0) * 1e6:.1f} us, wall {wall_ms * 1e3:.1f} us, "
+                  f"events {e0.elapsed_time(e1) * 1e3:.1f} us", file=sys.stderr)
         sync_all()
         ems = max(e0.elapsed_time(e1), wall_ms)
         if comm is not None:

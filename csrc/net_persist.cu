@@ -41,6 +41,7 @@
 // has consumed so the copy stream can reuse slots. The step's loss is stored by the kernel
 // straight into mapped pinned host memory (4 bytes device -> host per step).
 #include <cuda.h>
+#include <cstdlib>
 
 #include <atomic>
 #include <cstring>
@@ -1618,6 +1619,16 @@ static int feeder_launch(B200Feeder* f, const char* px, const long long* hy, int
   a.feed_base = f->fed;
   a.host_loss = dloss;
   a.epoch_begin = 0;
+  static const int pre_cfg = [] {
+    const char* e = getenv("B200DP_FEED_PRE");
+    const int v = e ? atoi(e) : 4;
+    return v < 0 ? 0 : (v > 16 ? 16 : v);
+  }();
+  const int pre_early = steps < pre_cfg ? steps : pre_cfg;
+  if (pre_early == 0) {       // kernel first: its start-up runs while the host enqueues the copies
+    if (int e = b200_net_persist_run(&a, f->compute)) return e;
+    ++f->launches;
+  }
   // labels: one or two contiguous pieces of the label ring
   {
     const unsigned pos = a.label_pos;
@@ -1633,9 +1644,9 @@ static int feeder_launch(B200Feeder* f, const char* px, const long long* hy, int
   // The first batches go up BEFORE the kernel is launched (the launch costs the host ~15 us,
   // during which the copy engines would otherwise sit idle); the kernel then finds its first
   // inputs in place, and the rest of the copies run ahead of it.
-  const int pre = steps < 4 ? steps : 4;
+  const int pre = steps < pre_cfg ? steps : pre_cfg;
   for (int i = 0; i < steps; ++i) {
-    if (i == pre) {
+    if (i == pre && pre > 0) {
       if (int e = b200_net_persist_run(&a, f->compute)) return e;
       ++f->launches;
     }
@@ -1652,7 +1663,7 @@ static int feeder_launch(B200Feeder* f, const char* px, const long long* hy, int
     CUP_OK(fn_cuStreamWriteValue32((CUstream)f->copy[p], (CUdeviceptr)(f->flags + 32u * p), g + 1u,
                                    CU_STREAM_WRITE_VALUE_DEFAULT));
   }
-  if (steps <= pre) {
+  if (steps <= pre && pre > 0) {
     if (int e = b200_net_persist_run(&a, f->compute)) return e;
     ++f->launches;
   }
