@@ -1196,6 +1196,15 @@ Plan choose(int M, int N, int K, bool rs_on, bool both_mn, bool allow_split) {
     return {0, bn, 1};
   }
   // automatic (thresholds from scripts/gemm_experiment.py on B200)
+  // A problem that fits ONE wave of one-tile CTAs (100..148 of them) runs fastest that way: no
+  // tile loop, no pair hand-shake (in-kernel times under ncu, profiles/r2/gemm_small_ncu.md:
+  // 512x4096x4096 25.3 us against 26.3 for persistent pairs, 4096x784x512 12.7 against 14.3).
+  {
+    const long long c256 = (long long)((M + 127) / 128) * ((N + 255) / 256);
+    const long long c128 = (long long)((M + 127) / 128) * ((N + 127) / 128);
+    if (!rs_on && N >= 256 && c256 >= 100 && c256 <= 148) return {0, 256, 1};
+    if (N >= 128 && c128 >= 100 && c128 <= 148) return {0, 128, 1};
+  }
   if (persist_ok) {
     if (N >= 256 && t256 >= 56) return {2, 256, 1};
     // Split-K (kind 3) is NOT chosen automatically: at 512 x 4096 x 4096 (32 tiles, 64 K
