@@ -1202,7 +1202,7 @@ Plan choose(int M, int N, int K, bool rs_on, bool both_mn, bool allow_split) {
   {
     const long long c256 = (long long)((M + 127) / 128) * ((N + 255) / 256);
     const long long c128 = (long long)((M + 127) / 128) * ((N + 127) / 128);
-    if (!rs_on && N >= 256 && c256 >= 100 && c256 <= 148) return {0, 256, 1};
+    if (!rs_on && N >= 256 && K <= 1024 && c256 >= 100 && c256 <= 148) return {0, 256, 1};   // measured at K = 512 only
     if (N >= 128 && c128 >= 100 && c128 <= 148) return {0, 128, 1};
   }
   if (persist_ok) {

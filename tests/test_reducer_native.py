@@ -52,8 +52,12 @@ def test_gemm_kernel_plan_host_only(native_lib):
         assert gemm.plan(4096, 4096, 512) == ("persistent", 256)        # fc2 wgrad
         assert gemm.plan(4096, 4096, 512, rs=True, both_mn=True) == ("persistent", 256)
         assert gemm.plan(4096, 784, 512, rs=True, both_mn=True) == ("persistent", 256)   # fc1 wgrad
-        assert gemm.plan(512, 4096, 4096) == ("persistent", 128)        # fc2 forward / dgrad
-        assert gemm.plan(512, 4096, 784) == ("persistent", 128)         # fc1 forward: K too short
+        # problems that fit one wave of 100-148 one-tile CTAs take the one-tile kernel
+        # (in-kernel times: profiles/r2/gemm_small_ncu.md)
+        assert gemm.plan(512, 4096, 4096) == ("cta", 128)               # fc2 forward / dgrad
+        assert gemm.plan(512, 4096, 784) == ("cta", 128)
+        assert gemm.plan(4096, 784, 512) == ("cta", 256)
+        assert gemm.plan(1024, 4096, 4096) == ("persistent", 256)       # long K: CTA pairs again
         # the reduce-scatter epilogue of other layouts stays on the one-CTA kernel
         assert gemm.plan(4096, 4096, 512, rs=True, both_mn=False) == ("cta", 128)
         # skinny problems: one CTA per tile, tile width follows N
