@@ -52,8 +52,11 @@ class LinearFn(torch.autograd.Function):
             dy = dy * (y > 0)
         dyv = dy[:, :n_out] if dy.shape[1] != n_out else dy   # cut padded logit columns
         dx = None
-        if ctx.needs_input_grad[0]:
-            # dgrad reads W, so it must be queued before the bucket kernel may update W
+        # Without ping-pong buffers dgrad reads the W that the bucket kernel updates, so it must
+        # be queued first. With them (DataParallel(pingpong=True)) the update goes to the other
+        # buffer: wgrad and the bucket's all-reduce start first and dgrad overlaps them.
+        late_dgrad = sink is not None and getattr(sink, "pingpong", False)
+        if ctx.needs_input_grad[0] and not late_dgrad:
             dx = gemm.linear_dgrad(dyv, W, relu_mask=x if mask_in else None)
         if sink is not None:
             rs = sink.rs_target(iw) if hasattr(sink, "rs_target") else None
@@ -67,6 +70,8 @@ class LinearFn(torch.autograd.Function):
             sink.ready(iw)
             sink.ready(ib)
             dW = db = None
+            if ctx.needs_input_grad[0] and late_dgrad:
+                dx = gemm.linear_dgrad(dyv, W, relu_mask=x if mask_in else None)
         else:
             dW = gemm.gemm_bf16(dyv, x, True, True)
             db = torch.empty(n_out, dtype=torch.bfloat16, device=x.device)
@@ -114,9 +119,13 @@ class WideMLP(nn.Module):
     def logits_padded(self, x: torch.Tensor) -> torch.Tensor:
         nl = len(self.layers)
         h = x
+        pp = self.sink is not None and getattr(self.sink, "pingpong", False)
         for i, lin in enumerate(self.layers):
             last = i == nl - 1
-            h = LinearFn.apply(h, lin.weight, lin.bias, not last, i > 0, not last, self.sink,
+            # ping-pong mode: this step's weights are in the buffer the last update wrote
+            W, b = (self.sink.live_param(2 * i), self.sink.live_param(2 * i + 1)) if pp \
+                else (lin.weight, lin.bias)
+            h = LinearFn.apply(h, W, b, not last, i > 0, not last, self.sink,
                                2 * i, 2 * i + 1, 16 if last else 0, last)
         return h
 

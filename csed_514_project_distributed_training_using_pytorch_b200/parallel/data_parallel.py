@@ -30,11 +30,17 @@ def module_bytes(module: nn.Module) -> int:
 
 class DataParallel(nn.Module):
     def __init__(self, module: nn.Module, comm=None, bucket_of: Optional[Sequence[int]] = None,
-                 fuse_sgd=None, algo="auto", broadcast_from: int = 0):
+                 fuse_sgd=None, algo="auto", broadcast_from: int = 0, pingpong: bool = False):
         """algo: "auto" | "oneshot" | "twoshot" | "nvls". "auto" (the default, like the
         reference's knob-free `DDP(model)`, src/train_dist.py:63) picks one-shot, two-shot or
         NVLS per bucket from the measured crossover table; "nvls" forces the in-switch reduction
-        and falls back to "twoshot" when the machine does not offer multicast."""
+        and falls back to "twoshot" when the machine does not offer multicast.
+        pingpong (needs fuse_sgd): two parameter buffers. Step t reads buffer t & 1 and the
+        bucket kernels write the updated weights into the other one, so a layer's weight
+        gradient and its bucket's all-reduce + update can be queued BEFORE the layer's data
+        gradient, which still reads the old weights (layers that know about it:
+        models/mlp.py). `live_param(i)` is parameter i as the current step must read it;
+        `sync_module()` copies the live buffer back into the module's own parameters."""
         super().__init__()
         if comm is None:
             from .process_group import get_comm
@@ -68,6 +74,13 @@ class DataParallel(nn.Module):
         self._require_backward_sync = True
         self._pass_open = False
         self._sunk = set()
+        self.pingpong = bool(pingpong) and fuse_sgd is not None and self.flat.param.is_cuda
+        self._live = 0
+        if self.pingpong:
+            self.param_alt = comm.alloc(self.flat.param.numel(), self.flat.param.dtype)
+            self.param_alt.copy_(self.flat.param)
+            self._alt_leaves = [v.requires_grad_(True) for v in self.flat.views(self.param_alt)]
+            self.reducer.update_target = self.param_alt      # step 0 reads flat.param
         for i, p in enumerate(self._params):
             if p.requires_grad:
                 p.register_post_accumulate_grad_hook(self._make_hook(i))
@@ -94,8 +107,28 @@ class DataParallel(nn.Module):
             self.reducer.mark_ready(i)
             if self.reducer.core.all_done():
                 self.reducer.finalize_backward()
-                self._pass_open = False
+                self._end_pass()
         return hook
+
+    def live_param(self, i: int) -> torch.Tensor:
+        """Parameter i in the buffer the current step reads (ping-pong mode)."""
+        return self._params[i] if self._live == 0 else self._alt_leaves[i]
+
+    def sync_module(self):
+        """Ping-pong mode: make the module's own parameters hold the live weights (before a
+        checkpoint or an evaluation that does not go through `live_param`)."""
+        if self.pingpong and self._live == 1:
+            if self.reducer.is_cuda:
+                torch.cuda.current_stream().wait_stream(self.reducer.stream)
+            self.flat.param.copy_(self.param_alt)
+            self._live = 0
+            self.reducer.update_target = self.param_alt
+
+    def _end_pass(self):
+        self._pass_open = False
+        if self.pingpong:       # the buckets of this pass wrote the other buffer: it is live now
+            self._live ^= 1
+            self.reducer.update_target = self.param_alt if self._live == 0 else self.flat.param
 
     def _begin_pass(self):
         if torch.is_grad_enabled() and self.training and self._require_backward_sync:
@@ -139,7 +172,7 @@ class DataParallel(nn.Module):
         self.reducer.mark_ready(i)
         if self.reducer.core.all_done():
             self.reducer.finalize_backward()
-            self._pass_open = False
+            self._end_pass()
 
     def finish_backward(self):
         """Call after `loss.backward()`: if a parameter received no gradient in this pass its
@@ -148,7 +181,7 @@ class DataParallel(nn.Module):
         bucket was launched from the hooks."""
         if self._pass_open:
             self.reducer.finalize_backward()
-            self._pass_open = False
+            self._end_pass()
 
     @contextlib.contextmanager
     def no_sync(self):

@@ -133,6 +133,7 @@ class Reducer:
         self.is_cuda = flat.param.is_cuda
         self.stream = torch.cuda.Stream(device=flat.param.device) if self.is_cuda else None
         self.fuse = fuse_sgd is not None
+        self.update_target = None      # set by DataParallel(pingpong=True)
         self.launched: List[int] = []
         self.sync_enabled = True
         self.kernel_launches = 0
@@ -235,9 +236,11 @@ class Reducer:
         with ctx:
             if self.fuse and self.is_cuda:
                 master, mom, base = self.state[b]
+                # ping-pong mode: the updated weights go to the buffer the step does NOT read
+                tgt = self.update_target if self.update_target is not None else self.flat.param
                 self.comm.all_reduce(g, op="mean", algo=algo, channel=b + 1,
                                      push_from=self.pushed.get(b, 0),
-                                     sgd=(self.flat.param[lo:hi], master, mom, self.hp, base))
+                                     sgd=(tgt[lo:hi], master, mom, self.hp, base))
             elif self.is_cuda:
                 self.comm.all_reduce(g, op="mean", algo=algo, channel=b + 1,
                                      push_from=self.pushed.get(b, 0))

@@ -344,10 +344,14 @@ def mlp_ddp(rank, world, backend, out_dir, algo):
     dev = comm.device
     torch.manual_seed(50 + rank)
     model = WideMLP((784, 256, 128, 10)).to(dev)
-    ddp = DP(model, comm, bucket_of=[2, 2, 1, 1, 0, 0], fuse_sgd=(0.1, 0.5, 0.0), algo=algo)
+    pingpong = algo.endswith("+pp")       # two parameter buffers: wgrad + bucket before dgrad
+    algo = algo.replace("+pp", "")
+    ddp = DP(model, comm, bucket_of=[2, 2, 1, 1, 0, 0], fuse_sgd=(0.1, 0.5, 0.0), algo=algo,
+             pingpong=pingpong)
     init = ddp.flat.param.clone().float().cpu()
     losses = []
-    for step in range(6):
+    nsteps = 5 if pingpong else 6         # odd: the live weights end up in the second buffer
+    for step in range(nsteps):
         g = torch.Generator().manual_seed(1000 * step + rank)
         x = torch.randn(32, 784, generator=g).to(torch.bfloat16).to(dev)
         y = torch.randint(0, 10, (32,), generator=g).to(dev)
@@ -355,6 +359,7 @@ def mlp_ddp(rank, world, backend, out_dir, algo):
         loss.backward()
         losses.append(loss)
     torch.cuda.current_stream().wait_stream(ddp.reducer.stream)
+    ddp.sync_module()                     # ping-pong: copy the live buffer into the module
     torch.cuda.synchronize()
     comm.check_errors()
     # fp32 master weights: whole buckets (one-shot) or this rank's shard of each (two-shot, NVLS)

@@ -65,9 +65,12 @@ def test_net_ddp_persistent_multistep_peer(native_lib, tmp_path):
         assert (p["losses"] > 1.5).all() and (p["losses"] < 3.5).all()
 
 
-@pytest.mark.parametrize("algo", ["oneshot", "twoshot", "nvls", "auto"])
+@pytest.mark.parametrize("algo", ["oneshot", "twoshot", "nvls", "auto", "twoshot+pp", "auto+pp"])
 def test_mlp_ddp_peer(native_lib, tmp_path, algo):
-    """bf16 MLP: replicas stay bit-identical; result tracks an fp32 single-process oracle."""
+    """bf16 MLP: replicas stay bit-identical; result tracks an fp32 single-process oracle.
+    "+pp": ping-pong parameter buffers (weight gradient and bucket kernel before the data
+    gradient), an odd number of steps so that the second buffer is the live one at the end."""
+    nsteps = 5 if algo.endswith("+pp") else 6
     from csed_514_project_distributed_training_using_pytorch_b200.models.mlp import WideMLP
     from csed_514_project_distributed_training_using_pytorch_b200.utils.flat import FlatParams
     world = _world()
@@ -96,7 +99,7 @@ def test_mlp_ddp_peer(native_lib, tmp_path, algo):
     ps = [v.clone() for v in flat.views(master)]
     bufs = [torch.zeros_like(p) for p in ps]
     B = 32
-    for step in range(6):
+    for step in range(nsteps):
         gs = [torch.zeros_like(p) for p in ps]
         Wq = [bf(p) for p in ps]
         for r in range(world):
