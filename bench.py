@@ -238,7 +238,8 @@ def run_ours(a):
                 done += m
             return outs
         wake_gpu(dev, 10.0)
-        host_steps(max(W, 3))
+        for _ in range(max(W, 3)):      # one call per warm-up step: the host path warms up as well
+            host_steps(1)
         sync_all()
         if comm is not None:
             comm.barrier()
@@ -254,6 +255,13 @@ def run_ours(a):
             import sys
             print(f"[bench debug] e2e: enqueue returned after {(t_enq - t0) * 1e6:.1f} us, wall {wall_ms * 1e3:.1f} us, "
                   f"events {e0.elapsed_time(e1) * 1e3:.1f} us", file=sys.stderr)
+            reps = []
+            for _ in range(5):
+                ta = time.perf_counter(); e0.record(); host_steps(K); tb = time.perf_counter()
+                e1.record(); torch.cuda.synchronize()
+                reps.append((round((tb - ta) * 1e6, 1), round((time.perf_counter() - ta) * 1e6, 1),
+                             round(e0.elapsed_time(e1) * 1e3, 1)))
+            print(f"[bench debug] e2e repeats (enqueue, wall, events): {reps}", file=sys.stderr)
         sync_all()
         ems = max(e0.elapsed_time(e1), wall_ms)
         if comm is not None:

@@ -41,7 +41,9 @@
 // has consumed so the copy stream can reuse slots. The step's loss is stored by the kernel
 // straight into mapped pinned host memory (4 bytes device -> host per step).
 #include <cuda.h>
+#include <cstdio>
 #include <cstdlib>
+#include <ctime>
 
 #include <atomic>
 #include <cstring>
@@ -1553,6 +1555,8 @@ struct B200Feeder {
   cudaStream_t compute, copy[2];
   cudaEvent_t join_in, join_compute, join_copy[2], labels_done;
   long long launches;
+  const float* hloss_lo;    // last pinned loss buffer and its device alias
+  float* dloss_lo;
 };
 
 int b200_feeder_create(const B200PersistHost* tmpl, int ring_slots, void** out) {
@@ -1598,6 +1602,19 @@ int b200_feeder_create(const B200PersistHost* tmpl, int ring_slots, void** out) 
 // copy (the images) and ONE 32-bit stream write (the step has landed), alternating between two
 // copy streams so two copy engines work at once; the labels of the whole launch go up in one
 // copy beforehand (they are 8 bytes per sample).
+// B200DP_FEED_TRACE=1: host timestamps (us since b200_feeder_run was entered) on stderr
+static bool feed_trace_on() {
+  static const bool on = [] { const char* e = getenv("B200DP_FEED_TRACE"); return e && atoi(e) != 0; }();
+  return on;
+}
+static double g_feed_t0 = 0.0;
+static double feed_now_us() {
+  timespec ts;
+  clock_gettime(CLOCK_MONOTONIC, &ts);
+  return ts.tv_sec * 1e6 + ts.tv_nsec * 1e-3;
+}
+#define FEED_TRACE(what) do { if (feed_trace_on()) fprintf(stderr, "[feed] %-28s %7.1f us\n", what, feed_now_us() - g_feed_t0); } while (0)
+
 static int feeder_launch(B200Feeder* f, const char* px, const long long* hy, int steps, float* dloss) {
   DRVP(cuStreamWriteValue32)
   DRVP(cuStreamWaitValue32)
@@ -1621,8 +1638,8 @@ static int feeder_launch(B200Feeder* f, const char* px, const long long* hy, int
   a.epoch_begin = 0;
   static const int pre_cfg = [] {
     const char* e = getenv("B200DP_FEED_PRE");
-    const int v = e ? atoi(e) : 4;
-    return v < 0 ? 0 : (v > 16 ? 16 : v);
+    const int v = e ? atoi(e) : 1;     // measured: 1 copy ahead of the launch is best (0: the launch
+    return v < 0 ? 0 : (v > 16 ? 16 : v);   // delays the first copy; 4: the copies delay the launch)
   }();
   const int pre_early = steps < pre_cfg ? steps : pre_cfg;
   if (pre_early == 0) {       // kernel first: its start-up runs while the host enqueues the copies
@@ -1641,14 +1658,17 @@ static int feeder_launch(B200Feeder* f, const char* px, const long long* hy, int
     B200_CUDA_OK(cudaEventRecord(f->labels_done, f->copy[0]));
     B200_CUDA_OK(cudaStreamWaitEvent(f->copy[1], f->labels_done, 0));
   }
+  FEED_TRACE("labels queued");
   // The first batches go up BEFORE the kernel is launched (the launch costs the host ~15 us,
   // during which the copy engines would otherwise sit idle); the kernel then finds its first
   // inputs in place, and the rest of the copies run ahead of it.
   const int pre = steps < pre_cfg ? steps : pre_cfg;
   for (int i = 0; i < steps; ++i) {
     if (i == pre && pre > 0) {
+      FEED_TRACE("first copies queued");
       if (int e = b200_net_persist_run(&a, f->compute)) return e;
       ++f->launches;
+      FEED_TRACE("kernel launched");
     }
     const unsigned g = f->fed + (unsigned)i;
     const unsigned p = g & 1u;
@@ -1678,18 +1698,31 @@ int b200_feeder_run(void* h, const void* hx, const long long* hy, int steps, flo
   B200Feeder* f = static_cast<B200Feeder*>(h);
   B200_REQUIRE(f && steps > 0, "b200_feeder_run: bad arguments");
   cudaStream_t cs = (cudaStream_t)caller_stream;
-  B200_CUDA_OK(cudaEventRecord(f->join_in, cs));
-  B200_CUDA_OK(cudaStreamWaitEvent(f->compute, f->join_in, 0));
-  for (int p = 0; p < 2; ++p) B200_CUDA_OK(cudaStreamWaitEvent(f->copy[p], f->join_in, 0));
+  // Order after the caller's stream. When that stream is idle there is nothing to order after
+  // (the previous run, which it waited for, has finished too): skip the four calls.
+  g_feed_t0 = feed_now_us();
+  const cudaError_t busy = cudaStreamQuery(cs);
+  if (busy != cudaSuccess) {
+    if (busy != cudaErrorNotReady) B200_CUDA_OK(busy);
+    B200_CUDA_OK(cudaEventRecord(f->join_in, cs));
+    B200_CUDA_OK(cudaStreamWaitEvent(f->compute, f->join_in, 0));
+    for (int p = 0; p < 2; ++p) B200_CUDA_OK(cudaStreamWaitEvent(f->copy[p], f->join_in, 0));
+  }
   float* dloss = nullptr;
   if (hloss) {
     // the kernel writes the losses into the caller's pinned buffer through its device alias
-    const cudaError_t e = cudaHostGetDevicePointer((void**)&dloss, hloss, 0);
-    if (e != cudaSuccess) {
-      (void)cudaGetLastError();
-      b200_set_error("b200_feeder_run: the loss buffer must be pinned (page-locked) host memory: %s",
-                     cudaGetErrorString(e));
-      return (int)e;
+    // (looked up once per buffer: callers reuse one pinned loss buffer)
+    if (hloss == f->hloss_lo) {
+      dloss = f->dloss_lo;
+    } else {
+      const cudaError_t e = cudaHostGetDevicePointer((void**)&dloss, hloss, 0);
+      if (e != cudaSuccess) {
+        (void)cudaGetLastError();
+        b200_set_error("b200_feeder_run: the loss buffer must be pinned (page-locked) host memory: %s",
+                       cudaGetErrorString(e));
+        return (int)e;
+      }
+      f->hloss_lo = hloss; f->dloss_lo = dloss;
     }
   }
   const char* px = static_cast<const char*>(hx);
@@ -1706,12 +1739,14 @@ int b200_feeder_run(void* h, const void* hx, const long long* hy, int steps, flo
       return e;
     done += n;
   }
+  FEED_TRACE("all copies queued");
   B200_CUDA_OK(cudaEventRecord(f->join_compute, f->compute));
   B200_CUDA_OK(cudaStreamWaitEvent(cs, f->join_compute, 0));
   for (int p = 0; p < 2; ++p) {
     B200_CUDA_OK(cudaEventRecord(f->join_copy[p], f->copy[p]));
     B200_CUDA_OK(cudaStreamWaitEvent(cs, f->join_copy[p], 0));
   }
+  FEED_TRACE("joined");
   return 0;
 }
 
