@@ -109,6 +109,8 @@ N.register_sigs({
 class WideMLP(nn.Module):
     """784-4096-4096-10 with ReLU between layers (BASELINE.json config 4)."""
 
+    supports_pingpong = True    # forward reads sink.live_param(i): see DataParallel(pingpong=True)
+
     def __init__(self, sizes: Sequence[int] = (784, 4096, 4096, 10), dtype=torch.bfloat16):
         super().__init__()
         self.sizes = tuple(sizes)

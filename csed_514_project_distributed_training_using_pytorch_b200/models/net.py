@@ -29,7 +29,12 @@ class Net(nn.Module):
 
     def __init__(self, dropout_seed: Optional[int] = None, conv2_impl: str = "simt"):
         super().__init__()
-        # "simt" (fp32-exact) or "tcgen05" (TF32 implicit GEMM on the tensor cores)
+        # conv2 of the layered CUDA path: "simt" (fp32-exact), "tc" (TF32 on tcgen05: implicit
+        # GEMM forward, data gradient and weight gradient, csrc/conv2_tc.cu), "auto" (the measured
+        # mix: tensor-core backward, tensor-core forward from batch 2048), "tcgen05" (the first
+        # tensor-core forward with an in-shared-memory im2col, kept for comparison)
+        if conv2_impl not in ("simt", "tc", "auto", "tcgen05"):
+            raise ValueError(f"conv2_impl must be simt, tc, auto or tcgen05, not {conv2_impl!r}")
         self.conv2_impl = conv2_impl
         # Parameter holders, registered in the reference's order (src/model.py:9-13) so that
         # the state_dict keys and the values drawn under a given torch seed are the same.

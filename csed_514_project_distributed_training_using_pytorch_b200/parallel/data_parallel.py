@@ -42,6 +42,12 @@ class DataParallel(nn.Module):
         models/mlp.py). `live_param(i)` is parameter i as the current step must read it;
         `sync_module()` copies the live buffer back into the module's own parameters."""
         super().__init__()
+        if pingpong and not getattr(module, "supports_pingpong", False):
+            # a module that reads its own nn.Parameters would never see the second buffer
+            raise ValueError("pingpong=True needs a module whose layers read their weights "
+                             "through sink.live_param() (models.mlp.WideMLP does)")
+        if pingpong and fuse_sgd is None:
+            raise ValueError("pingpong=True needs fuse_sgd: the bucket kernels write the other buffer")
         if comm is None:
             from .process_group import get_comm
             comm = get_comm()
@@ -74,7 +80,7 @@ class DataParallel(nn.Module):
         self._require_backward_sync = True
         self._pass_open = False
         self._sunk = set()
-        self.pingpong = bool(pingpong) and fuse_sgd is not None and self.flat.param.is_cuda
+        self.pingpong = bool(pingpong) and self.flat.param.is_cuda    # CPU/gloo: one buffer
         self._live = 0
         if self.pingpong:
             self.param_alt = comm.alloc(self.flat.param.numel(), self.flat.param.dtype)

@@ -749,9 +749,9 @@ int b200_conv2_dz_c32(const float* da2, const float* a2, const void* pos2, const
 
 // dw [20][10][5][5] and db [20] (both overwritten) from the two c32 operands (tcgen05, TF32
 // operands; the CTAs' partial sums meet in fp32 atomics).
-int b200_conv2_wgrad_tc(const float* a1_c4, const float* frame, float* dw, float* db, int B, void* stream) {
+int b200_conv2_wgrad_tc(const float* a1_c32, const float* dz_c32, float* dw, float* db, int B, void* stream) {
   B200_REQUIRE(B > 0, "b200_conv2_wgrad_tc: empty batch");
-  B200_REQUIRE((((uintptr_t)frame | (uintptr_t)a1_c4) & 511) == 0, "b200_conv2_wgrad_tc: operands must be 512-byte aligned");
+  B200_REQUIRE((((uintptr_t)dz_c32 | (uintptr_t)a1_c32) & 511) == 0, "b200_conv2_wgrad_tc: operands must be 512-byte aligned");
   static bool attr_done[64] = {false};
   int dev = 0;
   B200_CUDA_OK(cudaGetDevice(&dev));
@@ -761,7 +761,7 @@ int b200_conv2_wgrad_tc(const float* a1_c4, const float* frame, float* dw, float
   }
   B200_CUDA_OK(cudaMemsetAsync(dw, 0, W2_SZ * sizeof(float), (cudaStream_t)stream));
   B200_CUDA_OK(cudaMemsetAsync(db, 0, B2_SZ * sizeof(float), (cudaStream_t)stream));
-  conv2_wgrad_tc_kernel<<<B < 148 ? B : 148, CT_THREADS, WG_SMEM, (cudaStream_t)stream>>>(a1_c4, frame, dw, db, B);
+  conv2_wgrad_tc_kernel<<<B < 148 ? B : 148, CT_THREADS, WG_SMEM, (cudaStream_t)stream>>>(a1_c32, dz_c32, dw, db, B);
   B200_LAUNCH_OK();
   return 0;
 }

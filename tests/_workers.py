@@ -107,6 +107,11 @@ def ddp_generic(rank, world, backend, out_dir, fuse, algo):
     # three buckets (one per Linear) so overlap / ordering is exercised
     ddp = DP(model, comm, bucket_of=[2, 2, 1, 1, 0, 0],
              fuse_sgd=(0.05, 0.5, 0.0) if fuse else None, algo=algo)
+    try:    # ping-pong buffers are refused for a module that reads its own parameters
+        DP(model, comm, fuse_sgd=(0.05, 0.5, 0.0), pingpong=True)
+        raise AssertionError("pingpong=True was accepted for a plain nn.Module")
+    except ValueError:
+        pass
     init = ddp.flat.param.clone().cpu()
     opt = None if fuse else SGD(ddp.flat.param, ddp.flat.grad, lr=0.05, momentum=0.5)
     losses = []

@@ -257,3 +257,22 @@ def test_allreduce_algorithm_choice_includes_nvls():
     assert choose_from_table(2, 32 << 20, nvls_ok=True) == 1     # NVLS never won on two ranks
     assert choose_from_table(4, 2 << 20, nvls_ok=True) == 2      # four ranks: NVLS at 1-4 MiB
     assert choose_from_table(3, 2048) == 0                       # unmeasured world: nearest row
+
+
+def test_conv2_impl_option_is_validated_and_reaches_the_config():
+    """conv2_impl selects the tensor-core conv2 of the layered path (reference layer:
+    src/model.py:17); on the CPU every choice runs the same PyTorch oracle path."""
+    import argparse
+    assert TrainConfig().conv2_impl == "simt"
+    ns = add_config_args(argparse.ArgumentParser()).parse_args(["--conv2_impl", "auto"])
+    assert config_from_args(ns).conv2_impl == "auto"
+    with pytest.raises(ValueError):
+        Net(conv2_impl="wgmma")
+    torch.manual_seed(0)
+    x = torch.randn(4, 1, 28, 28)
+    outs = []
+    for impl in ("simt", "tc", "auto"):
+        torch.manual_seed(1)
+        net = Net(conv2_impl=impl).eval()
+        outs.append(net(x))
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
