@@ -1557,6 +1557,8 @@ struct B200Feeder {
   long long launches;
   const float* hloss_lo;    // last pinned loss buffer and its device alias
   float* dloss_lo;
+  cudaStream_t last_cs;     // caller stream of the previous run
+  bool last_cs_valid;
 };
 
 int b200_feeder_create(const B200PersistHost* tmpl, int ring_slots, void** out) {
@@ -1701,7 +1703,11 @@ int b200_feeder_run(void* h, const void* hx, const long long* hy, int steps, flo
   // Order after the caller's stream. When that stream is idle there is nothing to order after
   // (the previous run, which it waited for, has finished too): skip the four calls.
   g_feed_t0 = feed_now_us();
-  const cudaError_t busy = cudaStreamQuery(cs);
+  // (only for the stream the previous run was ordered into: its trailing joins are what tells
+  // us that run has finished)
+  const cudaError_t busy = (f->last_cs_valid && f->last_cs == cs) ? cudaStreamQuery(cs) : cudaErrorNotReady;
+  f->last_cs = cs;
+  f->last_cs_valid = true;
   if (busy != cudaSuccess) {
     if (busy != cudaErrorNotReady) B200_CUDA_OK(busy);
     B200_CUDA_OK(cudaEventRecord(f->join_in, cs));
