@@ -288,7 +288,6 @@ constexpr int CIPAD = 16;                               // 10 input channels pad
 constexpr int WD_TAP_BYTES = DZ_CHUNKS * CIPAD * 16;    // 1536
 constexpr int WD_BYTES = 25 * WD_TAP_BYTES;             // 38400
 constexpr int DG_STAGES = 3;
-constexpr int DG_SMEM = DG_STAGES * DZ_IMG_BYTES + WD_BYTES + 256 + 1024;
 // dZ frame [B][6][200][4] from the pooled gradient: one float4 (pixel, chunk) per thread.
 __global__ void conv2_dz_frame_kernel(const float* __restrict__ da2, const float* __restrict__ a2,
                                       const uint8_t* __restrict__ pos2, const float* __restrict__ mask,
@@ -337,17 +336,24 @@ __device__ __forceinline__ void bar_expect(uint64_t* bar, uint32_t bytes) {
 }
 
 // ---- data gradient -----------------------------------------------------------------------------
-// Persistent, one image per pipeline stage. warp 4 lane 0: bulk copies (the flipped weights once,
-// then one 19,200-byte dZ frame per image); warp 5 lane 0: 2 tiles x 25 taps x 3 K-steps of
-// tcgen05.mma.kind::tf32 (M=128, N=16, K=8), warp 6 lane 0 the same for the second tile;
+// Persistent, one image PAIR per pipeline stage: the two frames sit side by side in every chunk
+// plane ([chunk 6][image 2][200 pixels][4]), so the GEMM rows run through both images (rows
+// 0..143 image 0, 200..343 image 1, the rest unused) and three M tiles of 128 serve two images.
+// warp 4 lane 0: bulk copies (the flipped weights once, then 6 planes per image);
+// warps 5-7 lane 0: one M tile each, 25 taps x 3 K-steps of tcgen05.mma.kind::tf32 (M=128, N=16,
+// K=8) (the issue path of one thread, not the tensor pipe, bounds a stream of small MMAs);
 // warps 0-3: TMEM -> da1 [B][10][12][12].
+constexpr int DG_PLANE_BYTES = 2 * DZ_PLANE_BYTES;          // 6400: one chunk plane of a pair
+constexpr int DG_STAGE_BYTES = DZ_CHUNKS * DG_PLANE_BYTES;  // 38400
+constexpr int DG_PAIR_SMEM = DG_STAGES * DG_STAGE_BYTES + WD_BYTES + 256 + 1024;
+
 __global__ void __launch_bounds__(CT_THREADS, 1)
 conv2_dgrad_tc_kernel(const float* __restrict__ frame, const float* __restrict__ wd,
                       float* __restrict__ da1, int B) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  uint8_t* As = smem;                              // [stage][chunk 6][200 pixels][4 floats]
-  uint8_t* Bs = As + DG_STAGES * DZ_IMG_BYTES;     // [tap'][chunk 6][ci 16][4 floats]
+  uint8_t* As = smem;                              // [stage][chunk 6][image 2][200 pixels][4 floats]
+  uint8_t* Bs = As + DG_STAGES * DG_STAGE_BYTES;   // [tap'][chunk 6][ci 16][4 floats]
   uint64_t* bars = reinterpret_cast<uint64_t*>(Bs + WD_BYTES);
   uint64_t* a_full = bars;
   uint64_t* a_free = bars + DG_STAGES;
@@ -356,15 +362,16 @@ conv2_dgrad_tc_kernel(const float* __restrict__ frame, const float* __restrict__
   uint64_t* w_full = acc_free + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(w_full + 1);
   const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+  const int npairs = (B + 1) / 2;
 
   if (t == 0) {
-    for (int i = 0; i < DG_STAGES; ++i) { bar_init(a_full + i, 1); bar_init(a_free + i, 2); }
-    for (int i = 0; i < 2; ++i) { bar_init(acc_full + i, 2); bar_init(acc_free + i, 4); }
+    for (int i = 0; i < DG_STAGES; ++i) { bar_init(a_full + i, 1); bar_init(a_free + i, 3); }
+    for (int i = 0; i < 2; ++i) { bar_init(acc_full + i, 3); bar_init(acc_free + i, 4); }
     bar_init(w_full, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 64;" ::"r"(s32(tmem_slot)) : "memory");
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 128;" ::"r"(s32(tmem_slot)) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -377,59 +384,72 @@ conv2_dgrad_tc_kernel(const float* __restrict__ frame, const float* __restrict__
     bar_expect(w_full, WD_BYTES);
     bulk_load(Bs, wd, WD_BYTES, w_full);
     int it = 0;
-    for (int img = blockIdx.x; img < B; img += gridDim.x, ++it) {
+    for (int pair = blockIdx.x; pair < npairs; pair += gridDim.x, ++it) {
       const int st = it % DG_STAGES;
       if (it >= DG_STAGES) bar_wait(a_free + st, ((it / DG_STAGES) - 1) & 1);
-      bar_expect(a_full + st, DZ_IMG_BYTES);
-      bulk_load(As + st * DZ_IMG_BYTES, frame + (size_t)img * (DZ_IMG_BYTES / 4), DZ_IMG_BYTES, a_full + st);
+      const int nimg = (2 * pair + 1 < B) ? 2 : 1;
+      bar_expect(a_full + st, (uint32_t)(nimg * DZ_IMG_BYTES));
+      for (int im = 0; im < nimg; ++im) {
+        const float* src = frame + (size_t)(2 * pair + im) * (DZ_IMG_BYTES / 4);
+#pragma unroll
+        for (int c = 0; c < DZ_CHUNKS; ++c)
+          bulk_load(As + st * DG_STAGE_BYTES + c * DG_PLANE_BYTES + im * DZ_PLANE_BYTES,
+                    src + c * (DZ_PLANE_BYTES / 4), DZ_PLANE_BYTES, a_full + st);
+      }
     }
-  } else if ((warp == 5 || warp == 6) && lane == 0) {
-    // two issuing threads, one per M tile: the issue path of one thread, not the tensor pipe,
-    // bounds a stream of small MMAs; each commits its own MMAs to the (count 2) barriers
+  } else if (warp >= 5 && lane == 0) {
+    // three issuing threads, one per M tile; each commits its own MMAs to the (count 3) barriers
     constexpr uint32_t idesc = idesc_tf32(128, CIPAD);
-    const uint32_t b0 = s32(Bs);
     const int tile = warp - 5;
     bar_wait(w_full, 0);
+    const uint64_t bd0 = desc_k_noswz(s32(Bs), CIPAD * 16, 128);
     int it = 0;
-    for (int img = blockIdx.x; img < B; img += gridDim.x, ++it) {
+    for (int pair = blockIdx.x; pair < npairs; pair += gridDim.x, ++it) {
       const int buf = it & 1, st = it % DG_STAGES;
       if (it >= 2) bar_wait(acc_free + buf, ((it >> 1) - 1) & 1);
       bar_wait(a_full + st, (it / DG_STAGES) & 1);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-      const uint64_t bd0 = desc_k_noswz(b0, CIPAD * 16, 128);
-      {
-        const uint64_t ad0 = desc_k_noswz(s32(As + st * DZ_IMG_BYTES) + tile * (128 * 16), DZ_PLANE_BYTES, 128);
-        const uint32_t d = tmem + (buf * 2 + tile) * CIPAD;
+      const uint64_t ad0 = desc_k_noswz(s32(As + st * DG_STAGE_BYTES) + tile * (128 * 16), DG_PLANE_BYTES, 128);
+      const uint32_t d = tmem + buf * 64 + tile * CIPAD;
 #pragma unroll
-        for (int tp = 0; tp < 25; ++tp) {
-          const int ky = tp / 5, kx = tp - ky * 5;
+      for (int tp = 0; tp < 25; ++tp) {
+        const int ky = tp / 5, kx = tp - ky * 5;
 #pragma unroll
-          for (int kc = 0; kc < 3; ++kc)
-            mma_tf32(d, desc_advance(ad0, (ky * 12 + kx) * 16 + (2 * kc) * DZ_PLANE_BYTES),
-                     desc_advance(bd0, tp * WD_TAP_BYTES + (2 * kc) * (CIPAD * 16)), idesc, (tp | kc) ? 1u : 0u);
-        }
+        for (int kc = 0; kc < 3; ++kc)
+          mma_tf32(d, desc_advance(ad0, (ky * 12 + kx) * 16 + (2 * kc) * DG_PLANE_BYTES),
+                   desc_advance(bd0, tp * WD_TAP_BYTES + (2 * kc) * (CIPAD * 16)), idesc, (tp | kc) ? 1u : 0u);
       }
       mma_commit(a_free + st);
       mma_commit(acc_full + buf);
     }
   } else if (warp < 4) {
-    // lane l of warp w: row 32w + l of tile 0 (columns 0..15) and of tile 1 (columns 16..31)
+    // lane l of warp w holds row 32w + l of each tile: tile 0 in columns 0..15, tile 1 in 16..31,
+    // tile 2 in 32..47 of the buffer
     int it = 0;
-    for (int img = blockIdx.x; img < B; img += gridDim.x, ++it) {
+    for (int pair = blockIdx.x; pair < npairs; pair += gridDim.x, ++it) {
       const int buf = it & 1;
       bar_wait(acc_full + buf, (it >> 1) & 1);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-      uint32_t r[32];
-      tmem_ld32(tmem + buf * 2 * CIPAD + ((uint32_t)(warp * 32) << 16), r);
+      uint32_t r[32], r2[32];
+      tmem_ld32(tmem + buf * 64 + ((uint32_t)(warp * 32) << 16), r);
+      tmem_ld32(tmem + buf * 64 + 32 + ((uint32_t)(warp * 32) << 16), r2);
       asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
       __syncwarp();
       if (lane == 0) bar_arrive(acc_free + buf);
-      float* out = da1 + (size_t)img * A1_SZ;
-      const int q0 = warp * 32 + lane, q1 = 128 + q0;
+      const bool two = 2 * pair + 1 < B;
+      float* out0 = da1 + (size_t)(2 * pair) * A1_SZ;
+      float* out1 = out0 + A1_SZ;
+      const int row0 = warp * 32 + lane, row1 = 128 + row0, row2 = 256 + row0;
+      // tile 1: rows 128..143 finish image 0, rows 200..255 start image 1; tile 2: rows 256..343
+      float* o1 = nullptr;
+      if (row1 < 144) o1 = out0 + row1;
+      else if (row1 >= FRAME && two) o1 = out1 + (row1 - FRAME);
+      float* o2 = (two && row2 - FRAME < 144) ? out1 + (row2 - FRAME) : nullptr;
 #pragma unroll
       for (int ci = 0; ci < C1; ++ci) {
-        out[ci * 144 + q0] = __uint_as_float(r[ci]);
-        if (q1 < 144) out[ci * 144 + q1] = __uint_as_float(r[CIPAD + ci]);
+        out0[ci * 144 + row0] = __uint_as_float(r[ci]);
+        if (o1) o1[ci * 144] = __uint_as_float(r[CIPAD + ci]);
+        if (o2) o2[ci * 144] = __uint_as_float(r2[ci]);
       }
     }
   }
@@ -437,7 +457,7 @@ conv2_dgrad_tc_kernel(const float* __restrict__ frame, const float* __restrict__
   __syncthreads();
   if (warp == 1) {
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 64;" ::"r"(tmem) : "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 128;" ::"r"(tmem) : "memory");
   }
 }
 
@@ -716,10 +736,11 @@ int b200_conv2_dgrad_tc(const float* frame, const float* wd, float* da1, int B, 
   int dev = 0;
   B200_CUDA_OK(cudaGetDevice(&dev));
   if (!attr_done[dev & 63]) {
-    B200_CUDA_OK(cudaFuncSetAttribute(conv2_dgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DG_SMEM));
+    B200_CUDA_OK(cudaFuncSetAttribute(conv2_dgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DG_PAIR_SMEM));
     attr_done[dev & 63] = true;
   }
-  conv2_dgrad_tc_kernel<<<B < 148 ? B : 148, CT_THREADS, DG_SMEM, (cudaStream_t)stream>>>(frame, wd, da1, B);
+  const int npairs = (B + 1) / 2;
+  conv2_dgrad_tc_kernel<<<npairs < 148 ? npairs : 148, CT_THREADS, DG_PAIR_SMEM, (cudaStream_t)stream>>>(frame, wd, da1, B);
   B200_LAUNCH_OK();
   return 0;
 }
