@@ -475,8 +475,8 @@ conv2_dgrad_tc_kernel(const float* __restrict__ frame, const float* __restrict__
 //     B = dZ  [96 pixels][32]:  pitch-12 rows y = 0..7, x = 8..11 zero, channels 20..31 zero
 // A's LBO is ONE pixel row: the four 32-channel groups of M = 128 are four consecutive shifts
 // j0..j0+3 of the image, so one MMA yields dW[:, :, ky, kx..kx+3] (j0 = ky*12 + kx); ten
-// accumulators (5 filter rows x {kx 0..3, kx 4}) cover the filter. Per image: 12 K-steps of 8
-// pixels x 10 tcgen05.mma (M=128, N=32, K=8). The CTAs' sums meet in fp32 atomics.
+// accumulators (5 filter rows x {kx 0..3, kx 4}) cover the filter. Per image: 8 K-steps (one per dZ
+// row: its 8 real pixels) x 10 tcgen05.mma (M=128, N=32, K=8). The CTAs' sums meet in fp32 atomics.
 constexpr int C32_A1_PIX = 160;
 constexpr int C32_A1_BYTES = C32_A1_PIX * 128;          // 20480
 constexpr int C32_DZ_PIX = 96;
@@ -581,11 +581,12 @@ conv2_wgrad_tc_kernel(const float* __restrict__ a1_c32, const float* __restrict_
       const uint32_t a0 = s32(St + st * WG_STAGE_BYTES);
       const uint64_t ad0 = desc_mn_sw32atom(a0, 128, 512);                    // LBO = one pixel
       const uint64_t bd0 = desc_mn_sw32atom(a0 + C32_A1_BYTES, 128, 512);     // N = 32: one group
+      // one K-step per dZ row: its 8 real pixels (the row's other 4 are zero and are skipped)
 #pragma unroll 2
-      for (int ks = 0; ks < 12; ++ks) {
+      for (int ks = 0; ks < 8; ++ks) {
         const uint32_t acc = (it > 0 || ks > 0) ? 1u : 0u;
-        const uint64_t bd = desc_advance(bd0, ks * 1024);
-        const uint64_t adk = desc_advance(ad0, ks * 1024);
+        const uint64_t bd = desc_advance(bd0, ks * (12 * 128));
+        const uint64_t adk = desc_advance(ad0, ks * (12 * 128));
 #pragma unroll
         for (int i = 0; i < 5; ++i) {
           const int a = abase + i;
