@@ -53,6 +53,7 @@ _SIGS = {
     "b200_conv2_c32_dz_floats": [c_i],
     "b200_a1_to_c32": [c_p, c_p, c_i, c_p],
     "b200_conv2_dz_c32": [c_p, c_p, c_p, c_p, c_p, c_i, c_p],
+    "b200_conv2_dz_both": [c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_p],
     "b200_conv2_fwd_tc2": [c_p, c_p, c_p, c_p, c_i, c_f, c_ull, c_ull, c_p, c_p, c_i, c_p],
     "b200_conv2_bwd": [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_p],
     "b200_fc1_fwd": [c_p, c_p, c_p, c_p, c_i, c_f, c_ull, c_ull, c_p, c_i, c_p],

@@ -88,7 +88,7 @@ class Conv2DropPoolRelu(torch.autograd.Function):
         # "tcgen05": the first tensor-core version with an in-smem im2col (csrc/conv_tcgen05.cu);
         # "simt": fp32-exact CUDA-core kernel (csrc/net_kernels.cu)
         # "auto": the measured choice for the layered path (profiles/r2/conv2_bwd_bench.json,
-        #         conv2_tc_bench.json): tensor-core backward always (5-9x the SIMT kernel),
+        #         conv2_tc_bench.json): tensor-core backward always (7-14x the SIMT kernel),
         #         tensor-core forward from batch 2048 up
         fwd_tc = impl == "tc" or (impl == "auto" and B >= 2048)
         if fwd_tc:
@@ -130,14 +130,19 @@ def _conv2_backward_tc(ctx, a1, w, a2, pos2, mask, da2):
     c32 = torch.empty(lib.b200_conv2_c32_a1_floats(B), dtype=torch.float32, device=dev)
     dz32 = torch.empty(lib.b200_conv2_c32_dz_floats(B), dtype=torch.float32, device=dev)
     N.call("b200_a1_to_c32", N.ptr(a1), N.ptr(c32), B, N.stream())
-    N.call("b200_conv2_dz_c32", N.ptr(da2), N.ptr(a2), N.ptr(pos2), N.ptr(mask), N.ptr(dz32), B, N.stream())
+    need_da1 = bool(ctx.needs_input_grad[0])
+    frame = None
+    if need_da1:    # both dZ layouts from one pass over the pooled gradient
+        frame = torch.empty(lib.b200_conv2_frame_floats(B), dtype=torch.float32, device=dev)
+        N.call("b200_conv2_dz_both", N.ptr(da2), N.ptr(a2), N.ptr(pos2), N.ptr(mask), N.ptr(frame),
+               N.ptr(dz32), B, N.stream())
+    else:
+        N.call("b200_conv2_dz_c32", N.ptr(da2), N.ptr(a2), N.ptr(pos2), N.ptr(mask), N.ptr(dz32), B, N.stream())
     dw = torch.empty_like(w)
     db = torch.empty(20, dtype=torch.float32, device=dev)
     N.call("b200_conv2_wgrad_tc", N.ptr(c32), N.ptr(dz32), N.ptr(dw), N.ptr(db), B, N.stream())
     da1 = None
-    if ctx.needs_input_grad[0]:
-        frame = torch.empty(lib.b200_conv2_frame_floats(B), dtype=torch.float32, device=dev)
-        N.call("b200_conv2_dz_frame", N.ptr(da2), N.ptr(a2), N.ptr(pos2), N.ptr(mask), N.ptr(frame), B, N.stream())
+    if need_da1:
         wd = torch.empty(lib.b200_conv2_dgrad_operand_floats(), dtype=torch.float32, device=dev)
         N.call("b200_conv2_w_to_dgrad_operand", N.ptr(w), N.ptr(wd), N.stream())
         da1 = torch.empty(B, 10, 12, 12, dtype=torch.float32, device=dev)

@@ -532,6 +532,40 @@ __global__ void conv2_dz_c32_kernel(const float* __restrict__ da2, const float* 
   dst[1] = make_float4(v[4], v[5], v[6], v[7]);
 }
 
+// Both dZ layouts of one image from one pass over its pooled gradient: the 320 values are
+// scattered into shared-memory images of the frame (data gradient) and of the c32 operand (weight
+// gradient), which then go out as coalesced 16-byte stores. One CTA per image.
+constexpr int DZ_BOTH_THREADS = 256;
+__global__ void __launch_bounds__(DZ_BOTH_THREADS)
+conv2_dz_both_kernel(const float* __restrict__ da2, const float* __restrict__ a2,
+                     const uint8_t* __restrict__ pos2, const float* __restrict__ mask,
+                     float* __restrict__ frame, float* __restrict__ dz32, int B) {
+  __shared__ __align__(16) float fs[DZ_IMG_BYTES / 4];     // [chunk 6][200 pixels][4]
+  __shared__ __align__(16) float cs[C32_DZ_BYTES / 4];     // [96 pixels][32], swizzled
+  const int t = threadIdx.x;
+  for (int img = blockIdx.x; img < B; img += gridDim.x) {
+    for (int i = t; i < DZ_IMG_BYTES / 16; i += DZ_BOTH_THREADS)
+      reinterpret_cast<float4*>(fs)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int i = t; i < C32_DZ_BYTES / 16; i += DZ_BOTH_THREADS)
+      reinterpret_cast<float4*>(cs)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    __syncthreads();
+    for (int i = t; i < A2_SZ; i += DZ_BOTH_THREADS) {      // one pooled value per thread
+      const size_t gi = (size_t)img * A2_SZ + i;
+      const int co = i >> 4;
+      const float v = (a2[gi] > 0.0f) ? da2[gi] * (mask ? mask[(size_t)img * C2 + co] : 1.0f) : 0.0f;
+      const int q = pos2[gi];                               // y*12 + x of the window's arg-max
+      fs[((co >> 2) * FRAME + DZ_ORIGIN + q) * 4 + (co & 3)] = v;
+      cs[q * 32 + (((co >> 3) ^ (q & 3)) * 8) + (co & 7)] = v;
+    }
+    __syncthreads();
+    float4* fo = reinterpret_cast<float4*>(frame + (size_t)img * (DZ_IMG_BYTES / 4));
+    for (int i = t; i < DZ_IMG_BYTES / 16; i += DZ_BOTH_THREADS) fo[i] = reinterpret_cast<const float4*>(fs)[i];
+    float4* co4 = reinterpret_cast<float4*>(dz32 + (size_t)img * (C32_DZ_BYTES / 4));
+    for (int i = t; i < C32_DZ_BYTES / 16; i += DZ_BOTH_THREADS) co4[i] = reinterpret_cast<const float4*>(cs)[i];
+    __syncthreads();
+  }
+}
+
 __global__ void __launch_bounds__(CT_THREADS, 1)
 conv2_wgrad_tc_kernel(const float* __restrict__ a1_c32, const float* __restrict__ dz_c32,
                       float* __restrict__ dw, float* __restrict__ db, int B) {
@@ -765,6 +799,16 @@ int b200_conv2_dz_c32(const float* da2, const float* a2, const void* pos2, const
   const int n = B * C32_DZ_PIX * 4;
   conv2_dz_c32_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(da2, a2, (const uint8_t*)pos2,
                                                                          mask, dz, B);
+  B200_LAUNCH_OK();
+  return 0;
+}
+
+// Both dZ layouts in one pass (what b200_conv2_dz_frame + b200_conv2_dz_c32 produce).
+int b200_conv2_dz_both(const float* da2, const float* a2, const void* pos2, const float* mask,
+                       float* frame, float* dz_c32, int B, void* stream) {
+  if (B <= 0) return 0;
+  conv2_dz_both_kernel<<<B < 148 * 4 ? B : 148 * 4, DZ_BOTH_THREADS, 0, (cudaStream_t)stream>>>(
+      da2, a2, (const uint8_t*)pos2, mask, frame, dz_c32, B);
   B200_LAUNCH_OK();
   return 0;
 }

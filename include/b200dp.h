@@ -233,6 +233,8 @@ int b200_conv2_c32_dz_floats(int B);
 int b200_a1_to_c32(const float* a1, float* c32, int B, void* stream);
 int b200_conv2_dz_c32(const float* da2, const float* a2, const void* pos2, const float* mask,
                       float* dz, int B, void* stream);
+int b200_conv2_dz_both(const float* da2, const float* a2, const void* pos2, const float* mask,
+                       float* frame, float* dz_c32, int B, void* stream);   /* frame + c32 in one pass */
 int b200_conv2_wgrad_tc(const float* a1_c32, const float* dz_c32, float* dw, float* db, int B, void* stream);
 /* MLP helpers: fused softmax + NLL + gradient, bias gradient, master-weight SGD. */
 int b200_softmax_nll_bf16(const float* logits, int ld, int ncls, const long long* labels,

@@ -57,6 +57,7 @@ for B in ((int(os.environ.get('NCU_B', '1000')),) if only else (64, 256, 512, 10
         "dz_c32": lambda: N.call("b200_conv2_dz_c32", N.ptr(da2), N.ptr(a2), N.ptr(pos2), None, N.ptr(dz32), B, s),
         "wgrad_tc": lambda: N.call("b200_conv2_wgrad_tc", N.ptr(c32), N.ptr(dz32), N.ptr(dw), N.ptr(db), B, s),
         "dz_frame": lambda: N.call("b200_conv2_dz_frame", N.ptr(da2), N.ptr(a2), N.ptr(pos2), None, N.ptr(frame), B, s),
+        "dz_both": lambda: N.call("b200_conv2_dz_both", N.ptr(da2), N.ptr(a2), N.ptr(pos2), None, N.ptr(frame), N.ptr(dz32), B, s),
         "w_to_dgrad_operand": lambda: N.call("b200_conv2_w_to_dgrad_operand", N.ptr(w), N.ptr(wd), s),
         "dgrad_tc": lambda: N.call("b200_conv2_dgrad_tc", N.ptr(frame), N.ptr(wd), N.ptr(da1), B, s),
     }
@@ -67,7 +68,8 @@ for B in ((int(os.environ.get('NCU_B', '1000')),) if only else (64, 256, 512, 10
         torch.cuda.synchronize()
         continue
     row = {k + "_us": timed(f) for k, f in calls.items()}
-    row["tc_bwd_total_us"] = round(sum(v for k, v in row.items() if not k.startswith("simt")), 2)
+    row["tc_bwd_total_us"] = round(sum(v for k, v in row.items()
+                                      if not k.startswith(("simt", "dz_c32", "dz_frame"))), 2)   # dz_both replaces the two
     out[B] = row
     print(B, row, flush=True)
 res = {"what": "conv2 backward (dw, db, da1) per native call; wgrad_tc includes its two memsets",
